@@ -1,0 +1,177 @@
+/*
+ * pi0b200.h - C ABI of the B200-native Pi0 `infer_action` hot path (libpi0b200.so).
+ *
+ * The reference (chenbadream/INT-ACT) is pure Python and has no FFI for this path; the entry points
+ * below are what a ctypes binding on the reference side binds in place of the PyTorch modules it
+ * calls today. Each entry cites the reference code it replaces (paths relative to the reference root;
+ * "[mirror]" = the in-tree derivative of the missing lerobot Pi0 source).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes only. Every device buffer (weights, workspace, inputs,
+ *     outputs) is owned by the caller (PyTorch); the library never allocates caller-visible memory.
+ *   - every function returns 0 on success and a negative code on failure; the message is available
+ *     from pi0_last_error() (thread-local).
+ *   - every launch goes to the cudaStream_t passed as `stream` (void* here to keep the header free of
+ *     CUDA includes). No entry point synchronises the device or allocates device memory, so
+ *     pi0_infer / pi0_denoise_loop can be captured in a CUDA graph.
+ *   - dtype: 0 = bf16 activations + weights (tcgen05 product path), 1 = fp32 check mode (SIMT).
+ *   - there is no CPU fallback anywhere behind this ABI.
+ */
+#ifndef PI0B200_H_
+#define PI0B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PI0_ABI_VERSION 1
+
+#define PI0_SIGLIP_LAYERS 27
+#define PI0_GEMMA_LAYERS 18
+
+/* ---- model geometry (config keys of config/models/pi0_finetune_bridge.json:34-48) -------------- */
+typedef struct pi0_model_cfg {
+  int32_t n_cams;         /* len(image_features) + empty cameras actually fed                      */
+  int32_t lang_len;       /* tokenizer_max_length                                                  */
+  int32_t horizon;        /* n_action_steps                                                        */
+  int32_t max_state_dim;  /* 32                                                                    */
+  int32_t max_action_dim; /* 32                                                                    */
+  int32_t num_steps;      /* flow-matching Euler steps (10)                                        */
+  int32_t dtype;          /* 0 = bf16, 1 = fp32 check mode                                         */
+  int32_t gemm_impl;      /* 0 = tcgen05 (bf16) / SIMT (fp32); 1 = force SIMT (debug cross-check)  */
+  int32_t max_batch;      /* workspace is carved for this many observations                        */
+  int32_t num_sms;        /* SM count of the device (persistent-grid size)                         */
+  int32_t skip_dead_work; /* 1 = skip the last prefill layer's attention/MLP (outputs discarded)  */
+  int32_t n_siglip_layers;/* <= PI0_SIGLIP_LAYERS (27 in the shipped model; fewer in depth-reduced tests) */
+  int32_t n_gemma_layers; /* <= PI0_GEMMA_LAYERS, shared by Gemma-2B and the action expert (18)     */
+  int32_t images_pre_normalized; /* 1 = skip prepare_images' img*2-1                 */
+  int32_t reserved[2];
+} pi0_model_cfg;
+
+/* ---- weights: packed by the host loader (int-act_b200/weights.py) into device tensors ----------
+ * W* matrices are [out, in] row-major in the activation dtype; biases and norm gains are fp32.    */
+typedef struct pi0_siglip_layer_w {
+  const float* ln1_w; const float* ln1_b;
+  const void* wqkv;   const float* bqkv;   /* [3456, 1152] q|k|v rows                               */
+  const void* wo;     const float* bo;     /* [1152, 1152]                                          */
+  const float* ln2_w; const float* ln2_b;
+  const void* wfc1;   const float* bfc1;   /* [4304, 1152]                                          */
+  const void* wfc2;   const float* bfc2;   /* [1152, 4304]                                          */
+} pi0_siglip_layer_w;
+
+typedef struct pi0_gemma_layer_w {
+  const float* g1;     /* 1 + input_layernorm.weight, fp32 [hidden]                                 */
+  const void* wqkv;    /* [8*256 + 256 + 256, hidden] q|k|v rows                                    */
+  const void* wo;      /* [hidden, 2048]                                                            */
+  const float* g2;     /* 1 + post_attention_layernorm.weight                                       */
+  const void* wgu;     /* [2*inter, hidden]: per 256 rows, 128 gate rows then the 128 matching up   */
+  const void* wdown;   /* [hidden, inter]                                                           */
+} pi0_gemma_layer_w;
+
+typedef struct pi0_weights {
+  /* SigLIP-So400m/14 + projector ([mirror] src/model/mvla/mllm.py:98-110,182-187) */
+  const void* patch_w;  const float* patch_b;   /* [1152, 592] (3*14*14 = 588 zero-padded to 592)  */
+  const void* pos_emb;                          /* [256, 1152] activation dtype                     */
+  pi0_siglip_layer_w sig[PI0_SIGLIP_LAYERS];
+  const float* post_ln_w; const float* post_ln_b;
+  const void* proj_w;   const float* proj_b;    /* [2048, 1152]                                     */
+  /* Gemma-2B ([mirror] mllm.py:86-97,193-249) */
+  const void* embed;                            /* [257152, 2048]                                   */
+  int64_t vocab;
+  pi0_gemma_layer_w gem[PI0_GEMMA_LAYERS];
+  /* action expert, Gemma-300M ([mirror] src/model/mvla/expert.py:70-93) */
+  pi0_gemma_layer_w exp[PI0_GEMMA_LAYERS];
+  const float* exp_norm_g;                      /* 1 + model.norm.weight                            */
+  /* projections ([mirror] src/model/mvla/modeling_mvla.py:538-543) */
+  const void* state_w;      const float* state_b;       /* [1024, 32]                               */
+  const void* action_in_w;  const float* action_in_b;   /* [1024, 32]                               */
+  const void* time_in_wa;                                /* [1024, 1024] action half of mlp_in      */
+  const float* time_bias;                                /* [num_steps, 1024] b + W_t . emb(t_k)    */
+  const void* time_out_w;   const float* time_out_b;    /* [1024, 1024]                             */
+  const void* action_out_w; const float* action_out_b;  /* [32, 1024]                               */
+  /* RoPE table ([mirror] mllm.py:30-53): cos/sin of pos / 10000^(2i/256), fp32 [max_pos, 128] */
+  const float* rope_cos; const float* rope_sin;
+  int32_t max_pos; int32_t reserved;
+} pi0_weights;
+
+typedef struct pi0_ctx pi0_ctx;
+
+int pi0_abi_version(void);
+const char* pi0_last_error(void);
+
+/* bytes of device workspace (activations + KV cache) needed for cfg->max_batch observations */
+size_t pi0_workspace_bytes(const pi0_model_cfg* cfg);
+
+/* Host-side context: records geometry, weight pointers and the carved workspace. No device work. */
+int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspace, size_t workspace_bytes,
+                   pi0_ctx** out);
+void pi0_ctx_destroy(pi0_ctx* ctx);
+
+/* SigLIP + projector for one camera: images f32 [B,3,224,224] -> prefix embedding rows
+ * [b, cam*256 .. cam*256+255]. `scale`/`shift` fuse prepare_images' img*2-1.
+ * Replaces PaliGemmaModel.embed_image + the two sqrt(2048) scalings
+ * ([mirror] mllm.py:182-187; modeling_mvla.py:366-367,596-601). */
+int pi0_siglip_forward(pi0_ctx* ctx, int B, int cam, const float* images, float scale, float shift, void* stream);
+
+/* Token embedding gather * sqrt(2048) into prefix rows [b, ncam*256 ..]
+ * ([mirror] mllm.py:189-191; modeling_mvla.py:612-616). tokens: int64 [B, lang_len] on device. */
+int pi0_embed_language(pi0_ctx* ctx, int B, const int64_t* tokens, void* stream);
+
+/* Gemma-2B prefill over the prefix: builds pad mask / position ids, runs the 18 layers and writes the
+ * KV cache in place. img_masks u8 [n_cams, B], lang_masks u8 [B, lang_len] on device.
+ * Replaces make_att_2d_masks + cumsum position ids + PaliGemmaWithExpertModel.forward(fill_kv_cache=True)
+ * ([mirror] modeling_mvla.py:98-128,765-766; mllm.py:193-249,265-317). */
+int pi0_prefill(pi0_ctx* ctx, int B, const uint8_t* img_masks, const uint8_t* lang_masks, void* stream);
+
+/* The flow-matching Euler loop: x_t f32 [B, horizon, max_action_dim] in/out (noise in, actions out),
+ * state f32 [B, max_state_dim]. Replaces embed_suffix + denoise_step + the while loop
+ * ([mirror] modeling_mvla.py:643-694,787-839). */
+int pi0_denoise_loop(pi0_ctx* ctx, int B, const float* state, float* x_t, void* stream);
+
+/* sample_actions end to end = siglip (per camera) + embed_language + prefill + denoise_loop
+ * ([mirror] modeling_mvla.py:753-804). images: n_cams device pointers (host array), each f32 [B,3,224,224]. */
+int pi0_infer(pi0_ctx* ctx, int B, const float* const* images, float img_scale, float img_shift,
+              const uint8_t* img_masks, const int64_t* tokens, const uint8_t* lang_masks, const float* state,
+              float* x_t, void* stream);
+
+/* Introspection for the parity tests (device pointers into the workspace; element type = cfg dtype) */
+const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems);
+
+/* kernels launched by this library since the last call with reset != 0 (bench "gpu_launches") */
+long long pi0_launch_count(int reset);
+
+/* ---- single-kernel entry points for unit tests ------------------------------------------------- */
+typedef struct pi0_gemm_desc {
+  const void* A; int64_t lda, a_z0, a_z1;
+  const void* W; int64_t ldw, w_z0, w_z1;
+  int32_t M, N, K, nz0, nz1;
+  int32_t epi_mode;  /* 0 store, 1 geglu, 2 rope(qkv), 3 euler */
+  int32_t bn;        /* 32 / 64 / 128 / 256 */
+  int32_t act;       /* 0 none, 1 gelu_tanh, 2 silu */
+  void* out; int64_t ldc, out_z0, out_z1;
+  const float* bias;
+  const void* res; int64_t ldr; int32_t res_row_mod;
+  float alpha, post_div, post_mul;
+  int32_t rpb_in, rpb_out, row_off;
+  void* vt; int32_t vt_col0, vt_hd, vt_heads, vt_rpb, vt_toff; int64_t vt_pitch;
+  const float* rope_cos; const float* rope_sin; const int32_t* pos_ids;
+  void* kcache; int32_t n_q_heads; int64_t kv_pitch;
+  float dt;
+} pi0_gemm_desc;
+
+/* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT. */
+int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream);
+
+int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream);
+int pi0_layernorm(const void* x, void* y, const float* w, const float* b, int M, int D, int dtype, void* stream);
+int pi0_softmax(void* scores, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
+                const uint8_t* pad, int pad_pitch, const int32_t* cum, int heads, int dtype, void* stream);
+int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PI0B200_H_ */

@@ -1,0 +1,67 @@
+// C-ABI entry points for single kernels (unit/parity tests call these through ctypes).
+// See include/pi0b200.h for the contract of every function.
+#include "../../include/pi0b200.h"
+#include "elementwise.cuh"
+
+using namespace pi0;
+
+extern "C" {
+
+int pi0_abi_version(void) { return PI0_ABI_VERSION; }
+const char* pi0_last_error(void) { return get_error(); }
+
+long long pi0_launch_count(int reset) {
+  long long v = g_launch_count;
+  if (reset) g_launch_count = 0;
+  return v;
+}
+
+int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream) {
+  PI0_REQUIRE(d != nullptr, "pi0_gemm: null descriptor");
+  GemmProblem g = gemm_problem(d->A, d->lda, d->W, d->ldw, d->M, d->N, d->K);
+  g.a_z0 = d->a_z0; g.a_z1 = d->a_z1; g.w_z0 = d->w_z0; g.w_z1 = d->w_z1;
+  g.nz0 = d->nz0 > 0 ? d->nz0 : 1;
+  g.nz1 = d->nz1 > 0 ? d->nz1 : 1;
+  g.epi_mode = d->epi_mode;
+  g.bn = d->bn;
+  EpiParams& e = g.epi;
+  e.out = d->out; e.ldc = d->ldc; e.out_z0 = d->out_z0; e.out_z1 = d->out_z1;
+  e.bias = d->bias; e.res = d->res; e.ldr = d->ldr; e.res_row_mod = d->res_row_mod;
+  e.alpha = d->alpha; e.post_div = d->post_div; e.post_mul = d->post_mul; e.act = d->act;
+  e.rpb_in = d->rpb_in; e.rpb_out = d->rpb_out; e.row_off = d->row_off;
+  if (d->vt != nullptr) {
+    e.vt = d->vt; e.vt_col0 = d->vt_col0; e.vt_hd = d->vt_hd; e.vt_heads = d->vt_heads;
+    e.vt_pitch = d->vt_pitch;
+  }
+  e.vt_rpb = d->vt_rpb > 0 ? d->vt_rpb : 1;
+  e.vt_toff = d->vt_toff;
+  e.rope_cos = d->rope_cos; e.rope_sin = d->rope_sin; e.pos_ids = d->pos_ids;
+  e.kcache = d->kcache; e.n_q_heads = d->n_q_heads; e.kv_pitch = d->kv_pitch;
+  e.dt = d->dt;
+  return gemm_launch(g, dtype, impl, num_sms, (cudaStream_t)stream);
+}
+
+int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream) {
+  if (dtype == 1) return rmsnorm<float>((const float*)x, (float*)y, g, M, D, 1e-6f, 0, 0, 0, (cudaStream_t)stream);
+  return rmsnorm<bf16>((const bf16*)x, (bf16*)y, g, M, D, 1e-6f, 0, 0, 0, (cudaStream_t)stream);
+}
+
+int pi0_layernorm(const void* x, void* y, const float* w, const float* b, int M, int D, int dtype, void* stream) {
+  if (dtype == 1) return layernorm<float>((const float*)x, (float*)y, w, b, M, D, 1e-6f, (cudaStream_t)stream);
+  return layernorm<bf16>((const bf16*)x, (bf16*)y, w, b, M, D, 1e-6f, (cudaStream_t)stream);
+}
+
+int pi0_softmax(void* scores, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
+                const uint8_t* pad, int pad_pitch, const int32_t* cum, int heads, int dtype, void* stream) {
+  if (dtype == 1)
+    return softmax_rows<float>((float*)scores, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum,
+                               heads, (cudaStream_t)stream);
+  return softmax_rows<bf16>((bf16*)scores, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads,
+                            (cudaStream_t)stream);
+}
+
+int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream) {
+  return position_ids(pad, B, P, S, prefix_pos, suffix_pos, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,27 @@
+// Launchers for the HBM-bound kernels (see elementwise.cu). T = bf16 (product) or float (check mode).
+#pragma once
+#include "gemm.cuh"
+
+namespace pi0 {
+
+template <typename T>
+int im2col_patch(const float* img, T* out, int B, int kpad, float scale, float shift, cudaStream_t s);
+template <typename T>
+int layernorm(const T* x, T* y, const float* w, const float* b, int M, int D, float eps, cudaStream_t s);
+template <typename T>
+int rmsnorm(const T* x, T* y, const float* g, int M, int D, float eps, int rpb_in, int rpb_out, int off,
+            cudaStream_t s);
+template <typename T>
+int softmax_rows(T* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
+                 const uint8_t* pad, int pad_pitch, const int* cum, int heads, cudaStream_t s);
+template <typename T>
+int embed_tokens(const int64_t* tok, const T* table, T* out, int B, int L, int P, int row_off, int D, int64_t vocab,
+                 float scale, cudaStream_t s);
+template <typename T>
+int cast_f32(const float* in, T* out, int64_t n, cudaStream_t s);
+
+int position_ids(const uint8_t* pad, int B, int P, int S, int* prefix_pos, int* suffix_pos, cudaStream_t s);
+int build_pad(const uint8_t* img_masks, const uint8_t* lang_masks, uint8_t* pad, int B, int ncam, int L,
+              cudaStream_t s);
+
+}  // namespace pi0

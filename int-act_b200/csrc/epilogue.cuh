@@ -1,0 +1,226 @@
+// GEMM epilogues shared by the tcgen05 kernel (bf16 regime) and the SIMT fp32 check-mode kernel.
+// Every epilogue consumes one 32-column fp32 accumulator chunk of one output row (the layout a
+// tcgen05.ld 32x32b gives each epilogue thread) and reproduces the reference's rounding points
+// (SURVEY.md §9.7): Linear output rounded to the activation type, then bias/residual/activation.
+#pragma once
+#include "common.cuh"
+
+namespace pi0 {
+
+enum EpiMode : int { EPI_STORE = 0, EPI_GEGLU = 1, EPI_ROPE = 2, EPI_EULER = 3 };
+enum ActKind : int { ACT_NONE = 0, ACT_GELU_TANH = 1, ACT_SILU = 2 };
+
+struct EpiParams {
+  void* out;            // activation type T, row-major
+  int64_t ldc;          // leading dimension of out (elements)
+  int64_t out_z0;       // batch strides of out (elements)
+  int64_t out_z1;
+  const float* bias;    // [N] fp32 or nullptr
+  const void* res;      // residual (type T) or nullptr
+  int64_t ldr;
+  int res_row_mod;      // residual row = row % res_row_mod when > 0 (SigLIP position embedding)
+  float alpha;          // t = rnd(t * alpha) when != 1 (attention scale)
+  float post_div;       // t = rnd(t / post_div) when != 0   (PaliGemma "/ sqrt(hidden)")
+  float post_mul;       // t = rnd(t * post_mul) when != 0   (Pi0 "* sqrt(hidden)")
+  int act;              // ActKind applied to the rounded Linear output
+  // output row remap: out_row = (row / rpb_in) * rpb_out + row_off + row % rpb_in (identity if rpb_in == 0)
+  int rpb_in, rpb_out, row_off;
+  // transposed region (V^T for the P.V GEMM): columns >= vt_col0 go to
+  //   vt[((b * vt_heads + h) * vt_hd + d) * vt_pitch + vt_toff + t],  b = row / vt_rpb, t = row % vt_rpb
+  void* vt;
+  int vt_col0, vt_hd, vt_heads, vt_rpb, vt_toff;
+  int64_t vt_pitch;
+  // EPI_ROPE (Gemma / expert fused QKV, one 256-wide head per N tile)
+  const float* rope_cos;  // [max_pos, 128]
+  const float* rope_sin;
+  const int* pos_ids;     // [M]
+  void* kcache;           // [B, kv_pitch, 256] type T
+  int n_q_heads;          // tiles [0, n_q_heads) are Q, then one K tile, then one V tile
+  int64_t kv_pitch;       // rows per sample in kcache
+  // EPI_EULER
+  float dt;
+};
+
+__host__ inline EpiParams epi_default() {
+  EpiParams e;
+  e.out = nullptr; e.ldc = 0; e.out_z0 = 0; e.out_z1 = 0; e.bias = nullptr; e.res = nullptr; e.ldr = 0;
+  e.res_row_mod = 0; e.alpha = 1.0f; e.post_div = 0.0f; e.post_mul = 0.0f; e.act = ACT_NONE;
+  e.rpb_in = 0; e.rpb_out = 0; e.row_off = 0;
+  e.vt = nullptr; e.vt_col0 = 0x7fffffff; e.vt_hd = 1; e.vt_heads = 1; e.vt_rpb = 1; e.vt_toff = 0; e.vt_pitch = 0;
+  e.rope_cos = nullptr; e.rope_sin = nullptr; e.pos_ids = nullptr; e.kcache = nullptr; e.n_q_heads = 0; e.kv_pitch = 0;
+  e.dt = 0.0f;
+  return e;
+}
+
+template <typename T>
+__device__ __forceinline__ void store8(T* dst, const float* v);
+template <>
+__device__ __forceinline__ void store8<bf16>(bf16* dst, const float* v) {
+  uint4 pk;
+  __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
+  __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
+  __nv_bfloat162 c = __floats2bfloat162_rn(v[4], v[5]);
+  __nv_bfloat162 d = __floats2bfloat162_rn(v[6], v[7]);
+  pk.x = *reinterpret_cast<uint32_t*>(&a);
+  pk.y = *reinterpret_cast<uint32_t*>(&b);
+  pk.z = *reinterpret_cast<uint32_t*>(&c);
+  pk.w = *reinterpret_cast<uint32_t*>(&d);
+  *reinterpret_cast<uint4*>(dst) = pk;
+}
+template <>
+__device__ __forceinline__ void store8<float>(float* dst, const float* v) {
+  *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <typename T>
+__device__ __forceinline__ void load8(const T* src, float* v);
+template <>
+__device__ __forceinline__ void load8<bf16>(const bf16* src, float* v) {
+  uint4 pk = *reinterpret_cast<const uint4*>(src);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+template <>
+__device__ __forceinline__ void load8<float>(const float* src, float* v) {
+  float4 a = *reinterpret_cast<const float4*>(src);
+  float4 b = *reinterpret_cast<const float4*>(src + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+__device__ __forceinline__ int64_t epi_out_row(const EpiParams& ep, int row) {
+  if (ep.rpb_in <= 0) return row;
+  return (int64_t)(row / ep.rpb_in) * ep.rpb_out + ep.row_off + (row % ep.rpb_in);
+}
+
+// ---- EPI_STORE: bias, alpha, post scale, activation, residual; optional transposed V region -----
+template <typename T>
+__device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, int col0, int N, int64_t zoff,
+                                                float* v) {
+  if (col0 >= ep.vt_col0) {  // V^T region: lanes of a warp hold consecutive t => coalesced per d
+    int b = row / ep.vt_rpb, t = row % ep.vt_rpb;
+    T* vt = reinterpret_cast<T*>(ep.vt);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      int col = col0 + j;
+      if (col < N) {
+        float x = v[j] + (ep.bias ? ep.bias[col] : 0.0f);
+        int dall = col - ep.vt_col0;
+        int h = dall / ep.vt_hd, d = dall % ep.vt_hd;
+        Num<T>::st(vt + ((int64_t)(b * ep.vt_heads + h) * ep.vt_hd + d) * ep.vt_pitch + ep.vt_toff + t, x);
+      }
+    }
+    return;
+  }
+  T* out = reinterpret_cast<T*>(ep.out) + zoff + epi_out_row(ep, row) * ep.ldc + col0;
+  const T* res = nullptr;
+  if (ep.res) {
+    int rrow = ep.res_row_mod > 0 ? row % ep.res_row_mod : row;
+    res = reinterpret_cast<const T*>(ep.res) + (int64_t)rrow * ep.ldr + col0;  // residuals are never batched
+  }
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    int col = col0 + g * 8;
+    if (col >= N) break;
+    float t[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float x = v[g * 8 + j];
+      if (ep.bias) x += ep.bias[col + j];
+      x = Num<T>::rnd(x);
+      if (ep.alpha != 1.0f) x = Num<T>::rnd(x * ep.alpha);
+      if (ep.post_div != 0.0f) x = Num<T>::rnd(x / ep.post_div);
+      if (ep.post_mul != 0.0f) x = Num<T>::rnd(x * ep.post_mul);
+      if (ep.act == ACT_GELU_TANH) x = Num<T>::rnd(gelu_tanh(x));
+      else if (ep.act == ACT_SILU) x = Num<T>::rnd(silu(x));
+      t[j] = x;
+    }
+    if (res) {
+      float r[8];
+      load8<T>(res + g * 8, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] += r[j];
+    }
+    store8<T>(out + g * 8, t);
+  }
+}
+
+// ---- EPI_GEGLU: out = gelu_tanh(gate) * up, gate/up interleaved per N tile at pack time ------------
+template <typename T>
+__device__ __forceinline__ void epi_geglu_chunk(const EpiParams& ep, int row, int out_col0, int n_out, float* gate,
+                                                const float* up) {
+  T* out = reinterpret_cast<T*>(ep.out) + epi_out_row(ep, row) * ep.ldc + out_col0;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    if (out_col0 + g * 8 >= n_out) break;
+    float t[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = Num<T>::rnd(gelu_tanh(Num<T>::rnd(gate[g * 8 + j])));
+      float u = Num<T>::rnd(up[g * 8 + j]);
+      t[j] = a * u;
+    }
+    store8<T>(out + g * 8, t);
+  }
+}
+
+// ---- EPI_ROPE: x1 = dims [c*32, c*32+32), x2 = the same + 128, of one 256-wide head ---------------
+// which: 0 = Q head `head`, 1 = K, 2 = V (V is not rotated; x1/x2 are stored as they are)
+template <typename T>
+__device__ __forceinline__ void epi_rope_chunk(const EpiParams& ep, int row, int which, int head, int c, float* x1,
+                                               float* x2) {
+  float o1[32], o2[32];
+  if (which < 2) {
+    int pos = ep.pos_ids[row];
+    const float* cs = ep.rope_cos + (int64_t)pos * 128 + c * 32;
+    const float* sn = ep.rope_sin + (int64_t)pos * 128 + c * 32;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      float a = Num<T>::rnd(x1[j]), b = Num<T>::rnd(x2[j]);
+      float cj = cs[j], sj = sn[j];
+      o1[j] = a * cj - b * sj;
+      o2[j] = b * cj + a * sj;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) { o1[j] = x1[j]; o2[j] = x2[j]; }
+  }
+  if (which == 0) {
+    T* out = reinterpret_cast<T*>(ep.out) + (int64_t)row * ep.ldc + head * 256 + c * 32;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) { store8<T>(out + g * 8, o1 + g * 8); store8<T>(out + 128 + g * 8, o2 + g * 8); }
+  } else {
+    int b = row / ep.vt_rpb, t = row % ep.vt_rpb;
+    if (which == 1) {
+      T* out = reinterpret_cast<T*>(ep.kcache) + ((int64_t)b * ep.kv_pitch + ep.vt_toff + t) * 256 + c * 32;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) { store8<T>(out + g * 8, o1 + g * 8); store8<T>(out + 128 + g * 8, o2 + g * 8); }
+    } else {
+      T* vt = reinterpret_cast<T*>(ep.vt) + (int64_t)b * 256 * ep.vt_pitch + ep.vt_toff + t;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        Num<T>::st(vt + (int64_t)(c * 32 + j) * ep.vt_pitch, o1[j]);
+        Num<T>::st(vt + (int64_t)(128 + c * 32 + j) * ep.vt_pitch, o2[j]);
+      }
+    }
+  }
+}
+
+// ---- EPI_EULER: x_t += rnd(dt * rnd(v_t)), x_t kept in fp32 (modeling_mvla.py:802) -----------------
+template <typename T>
+__device__ __forceinline__ void epi_euler_chunk(const EpiParams& ep, int row, int col0, int N, const float* v) {
+  float* x = reinterpret_cast<float*>(ep.out) + (int64_t)row * ep.ldc + col0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    if (col0 + j < N) {
+      float vt = Num<T>::rnd(v[j] + (ep.bias ? ep.bias[col0 + j] : 0.0f));
+      x[j] += Num<T>::rnd(ep.dt * vt);
+    }
+  }
+}
+
+}  // namespace pi0

@@ -1,0 +1,42 @@
+// Host-side description of one (optionally batched) GEMM  C[z][M,N] = A[z][M,K] . W[z][N,K]^T
+// with a fused epilogue. Both operands are K-major (nn.Linear weight layout), which is the layout
+// TMA + tcgen05 consume directly.
+#pragma once
+#include "epilogue.cuh"
+
+namespace pi0 {
+
+struct GemmProblem {
+  const void* A;
+  int64_t lda, a_z0, a_z1;  // elements
+  const void* W;
+  int64_t ldw, w_z0, w_z1;  // elements
+  int M, N, K;
+  int nz0, nz1;             // batch grid (1,1 for a plain GEMM)
+  int epi_mode;             // EpiMode
+  int bn;                   // N tile of the tcgen05 kernel (32/64/128/256); EPI_ROPE requires 256
+  EpiParams epi;
+};
+
+inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K) {
+  GemmProblem g;
+  g.A = A; g.lda = lda; g.a_z0 = 0; g.a_z1 = 0;
+  g.W = W; g.ldw = ldw; g.w_z0 = 0; g.w_z1 = 0;
+  g.M = M; g.N = N; g.K = K; g.nz0 = 1; g.nz1 = 1;
+  g.epi_mode = EPI_STORE; g.bn = 256;
+  g.epi = epi_default();
+  return g;
+}
+
+// dtype: 0 = bf16 activations/weights (tcgen05 path), 1 = fp32 check mode (SIMT path).
+// impl:  0 = default for the dtype, 1 = force the SIMT kernel (debug cross-check of the tcgen05 path).
+int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStream_t stream);
+
+int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream);
+template <typename T>
+int gemm_simt_launch(const GemmProblem& g, cudaStream_t stream);
+
+// number of tcgen05 GEMM / SIMT GEMM / other kernels launched since the last reset (bench "gpu_launches")
+extern long long g_launch_count;
+
+}  // namespace pi0

@@ -1,0 +1,300 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a:  C[z][M,N] = A[z][M,K] . W[z][N,K]^T, bf16 in, fp32 accumulate.
+//
+// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM owner),
+// warps 2..5 = epilogue (one TMEM lane quadrant each). Operand tiles are 128 x 64 (A) and BN x 64 (W),
+// K-major with the 128-byte swizzle that TMA writes and the UMMA smem descriptor reads.
+// The fp32 accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps
+// the main loop of tile i+1. Tiles are visited in groups of 8 M-tiles per N sweep to keep both operand
+// panels L2-resident. Replaces every nn.Linear / torch.matmul on the reference's hot path
+// (reference: src/model/mvla/mllm.py:216-242, 299-311).
+#include "gemm.cuh"
+
+namespace pi0 {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kGroupM = 8;
+constexpr int kTcThreads = 192;
+
+template <int BN>
+struct TcCfg {
+  static constexpr uint32_t kABytes = kBM * kBK * 2;
+  static constexpr uint32_t kBBytes = BN * kBK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
+  static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
+};
+
+struct TcShape {
+  int M, N, K;
+  int nz0, nz1;
+  int tiles_m, tiles_n;
+  int total_tiles;
+};
+
+__device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, int& tm, int& tn) {
+  int per_z = sh.tiles_m * sh.tiles_n;
+  z = idx / per_z;
+  int r = idx - z * per_z;
+  int span = kGroupM * sh.tiles_n;
+  int g = r / span;
+  int first_m = g * kGroupM;
+  int gsz = min(sh.tiles_m - first_m, kGroupM);
+  int rr = r - g * span;
+  tm = first_m + rr % gsz;
+  tn = rr / gsz;
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+               const EpiParams ep) {
+  using Cfg = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_k = (sh.K + kBK - 1) / kBK;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+        int z, tm, tn;
+        tile_coords(sh, idx, z, tm, tn);
+        const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
+          tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_k; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint64_t da = umma_desc_k_sw128(sa);
+          const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            // advancing 16 bf16 (32 B) along K inside the 128 B swizzle row: +2 in the (>>4) address field
+            umma_bf16(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == num_k - 1) umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else {
+    // ------------------------------ epilogue ----------------------------------
+    const int quad = warp & 3;  // TMEM lanes [32*quad, 32*quad+32) are the ones this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+      int z, tm, tn;
+      tile_coords(sh, idx, z, tm, tn);
+      const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+      const int row = tm * kBM + quad * 32 + lane;
+      const int n0 = tn * BN;
+      const bool row_ok = row < sh.M;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
+
+      if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
+        const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col0 = n0 + c * 32;
+          if (col0 >= sh.N) break;
+          float v[32];
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (row_ok) {
+            if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
+            else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
+          }
+        }
+      } else if constexpr (EPI == EPI_GEGLU) {
+        // tile columns [0, BN/2) are gate rows, [BN/2, BN) the matching up rows (interleaved at pack time)
+        const int n_out = sh.N / 2;
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int out_col0 = tn * (BN / 2) + c * 32;
+          if (out_col0 >= n_out) break;
+          float g[32], u[32];
+          tmem_ld_32x32(taddr + c * 32, g);
+          tmem_ld_32x32(taddr + BN / 2 + c * 32, u);
+          tmem_ld_wait();
+          if (row_ok) epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
+        }
+      } else if constexpr (EPI == EPI_ROPE) {
+        static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
+        const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          float x1[32], x2[32];
+          tmem_ld_32x32(taddr + c * 32, x1);
+          tmem_ld_32x32(taddr + 128 + c * 32, x2);
+          tmem_ld_wait();
+          if (row_ok) epi_rope_chunk<bf16>(ep, row, which, tn, c, x1, x2);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess || p == nullptr) {
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// rank-4 bf16 tensor map {k, rows, z0, z1}, box {64, box_rows, 1, 1}, 128 B swizzle, zero OOB fill
+static int make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0,
+                    int64_t sz1, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  PI0_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  PI0_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA operand base %p not 16-byte aligned", base);
+  PI0_REQUIRE((ld * 2) % 16 == 0, "TMA operand leading dimension %lld not a multiple of 8 elements", (long long)ld);
+  cuuint64_t gdim[4] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)nz0, (cuuint64_t)nz1};
+  cuuint64_t s1 = (cuuint64_t)ld * 2;
+  cuuint64_t s2 = nz0 > 1 ? (cuuint64_t)sz0 * 2 : s1;
+  cuuint64_t s3 = nz1 > 1 ? (cuuint64_t)sz1 * 2 : s1;
+  PI0_REQUIRE(s2 % 16 == 0 && s3 % 16 == 0, "TMA batch strides must be multiples of 8 elements");
+  cuuint64_t gstride[3] = {s1, s2, s3};
+  cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PI0_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d): K=%d rows=%d nz=%dx%d ld=%lld", (int)r, K, rows,
+              nz0, nz1, (long long)ld);
+  return 0;
+}
+
+template <int BN, int EPI>
+static int launch_cfg(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  using Cfg = TcCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, kBM));
+  PI0_TRY(make_map(&tmB, g.W, g.K, g.N, g.nz0, g.nz1, g.ldw, g.w_z0, g.w_z1, BN));
+  TcShape sh;
+  sh.M = g.M; sh.N = g.N; sh.K = g.K; sh.nz0 = g.nz0; sh.nz1 = g.nz1;
+  sh.tiles_m = (g.M + kBM - 1) / kBM;
+  sh.tiles_n = (g.N + BN - 1) / BN;
+  sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
+  int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
+  gemm_tc_kernel<BN, EPI><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, sh, g.epi);
+  PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  return 0;
+}
+
+int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
+  PI0_REQUIRE(g.N % 8 == 0 || g.epi_mode == EPI_EULER || g.epi.vt != nullptr, "gemm_tc: N=%d must be a multiple of 8", g.N);
+  switch (g.epi_mode) {
+    case EPI_STORE:
+      switch (g.bn) {
+        case 256: return launch_cfg<256, EPI_STORE>(g, num_sms, stream);
+        case 128: return launch_cfg<128, EPI_STORE>(g, num_sms, stream);
+        case 64: return launch_cfg<64, EPI_STORE>(g, num_sms, stream);
+        case 32: return launch_cfg<32, EPI_STORE>(g, num_sms, stream);
+      }
+      break;
+    case EPI_GEGLU:
+      PI0_REQUIRE(g.N % 256 == 0, "gemm_tc: GeGLU N=%d must be a multiple of 256", g.N);
+      if (g.bn == 256) return launch_cfg<256, EPI_GEGLU>(g, num_sms, stream);
+      break;
+    case EPI_ROPE:
+      PI0_REQUIRE(g.N == (g.epi.n_q_heads + 2) * 256, "gemm_tc: RoPE epilogue expects N = (q_heads + 2) * 256");
+      if (g.bn == 256) return launch_cfg<256, EPI_ROPE>(g, num_sms, stream);
+      break;
+    case EPI_EULER:
+      if (g.bn == 32) return launch_cfg<32, EPI_EULER>(g, num_sms, stream);
+      break;
+  }
+  set_error("gemm_tc: unsupported epilogue/tile combination epi=%d bn=%d", g.epi_mode, g.bn);
+  return -2;
+}
+
+}  // namespace pi0

@@ -1,0 +1,128 @@
+"""GPU unit tests of the GEMM kernels through the C ABI (pi0_gemm): the tcgen05/TMEM/TMA kernel (bf16) and the
+SIMT kernel (fp32 check mode / bf16 cross-check) against plain PyTorch fp32 references of the same op."""
+import math
+
+import pytest
+import torch
+
+from int_act_b200 import binding as pb
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref_linear(A, W):
+    return A.float() @ W.float().t()
+
+
+def _rand(shape, dev, scale=1.0, dtype=torch.bfloat16, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype).to(dev)
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("M,N,K,bn", [(128, 128, 64, 128), (300, 512, 256, 128), (5, 1024, 2048, 32),
+                                      (1000, 768, 1152, 256), (256, 72, 256, 128), (333, 2048, 4304, 64)])
+def test_gemm_plain_bf16(cuda, impl, M, N, K, bn):
+    A = _rand((M, K), cuda, seed=1)
+    W = _rand((N, K), cuda, 0.05, seed=2)
+    out = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(A, W, out, bn=bn, impl=impl)
+    torch.cuda.synchronize()
+    ref = _ref_linear(A, W)
+    err = (out.float() - ref).abs().max().item()
+    tol = 2e-2 * ref.abs().max().item() + 1e-3
+    assert err <= tol, (err, tol)
+
+
+def test_gemm_tc_matches_simt_exactly_enough(cuda):
+    A = _rand((700, 1024), cuda, seed=3)
+    W = _rand((640, 1024), cuda, 0.03, seed=4)
+    o0 = torch.zeros((700, 640), dtype=torch.bfloat16, device=cuda)
+    o1 = torch.zeros_like(o0)
+    pb.gemm(A, W, o0, bn=128, impl=0)
+    pb.gemm(A, W, o1, bn=128, impl=1)
+    torch.cuda.synchronize()
+    # both round one fp32 accumulator to bf16; only the fp32 summation order differs
+    assert (o0.float() - o1.float()).abs().max().item() <= 2 ** -7 * o1.float().abs().max().item()
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_bias_act_residual(cuda, impl):
+    M, N, K = 520, 1152, 512
+    A = _rand((M, K), cuda, seed=5)
+    W = _rand((N, K), cuda, 0.05, seed=6)
+    bias = _rand((N,), cuda, 0.5, torch.float32, seed=7)
+    res = _rand((M, N), cuda, seed=8)
+    out = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(A, W, out, bias=bias, res=res, act=pb.ACT_GELU_TANH, bn=128, impl=impl)
+    torch.cuda.synchronize()
+    lin = (_ref_linear(A, W) + bias).bfloat16().float()
+    ref = (torch.nn.functional.gelu(lin, approximate="tanh").bfloat16().float() + res.float()).bfloat16().float()
+    assert (out.float() - ref).abs().max().item() <= 5e-2
+
+
+def test_gemm_fp32_simt(cuda):
+    M, N, K = 333, 520, 588
+    A = _rand((M, K), cuda, dtype=torch.float32, seed=9)
+    W = _rand((N, K), cuda, 0.05, torch.float32, seed=10)
+    out = torch.zeros((M, N), dtype=torch.float32, device=cuda)
+    pb.gemm(A, W, out, dtype=pb.DTYPE_F32)
+    torch.cuda.synchronize()
+    ref = (A.double() @ W.double().t()).float()
+    assert (out - ref).abs().max().item() <= 1e-4
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_batched_heads(cuda, impl):
+    """scores[b,h] = q[b,:,h,:] . k[b,:,h,:]^T * scale with q,k strided views of one fused qkv buffer (SigLIP)."""
+    B, T, H, D = 3, 256, 16, 72
+    qkv = _rand((B, T, 3 * H * D), cuda, seed=11)
+    sc = torch.zeros((B, H, T, T), dtype=torch.bfloat16, device=cuda)
+    q = qkv[..., : H * D]
+    k = qkv[..., H * D: 2 * H * D]
+    pb.gemm(q, k, sc, M=T, N=T, K=D, lda=3 * H * D, ldw=3 * H * D, ldc=T, nz0=H, nz1=B,
+            a_z=(D, T * 3 * H * D), w_z=(D, T * 3 * H * D), out_z=(T * T, H * T * T), alpha=D ** -0.5, bn=128,
+            impl=impl)
+    torch.cuda.synchronize()
+    qf = q.float().view(B, T, H, D).permute(0, 2, 1, 3)
+    kf = k.float().view(B, T, H, D).permute(0, 2, 1, 3)
+    ref = ((qf @ kf.transpose(2, 3)).bfloat16().float() * D ** -0.5).bfloat16().float()
+    assert (sc.float() - ref).abs().max().item() <= 3e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_gemm_geglu(cuda, impl):
+    M, K, inter = 200, 1024, 512
+    A = _rand((M, K), cuda, seed=12)
+    Wg = _rand((inter, K), cuda, 0.03, seed=13)
+    Wu = _rand((inter, K), cuda, 0.03, seed=14)
+    # pack: per 256 rows, 128 gate rows then the matching 128 up rows
+    Wgu = torch.stack([Wg.view(-1, 128, K), Wu.view(-1, 128, K)], dim=1).reshape(2 * inter, K).contiguous()
+    out = torch.zeros((M, inter), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(A, Wgu, out, epi_mode=pb.EPI_GEGLU, bn=256, impl=impl)
+    torch.cuda.synchronize()
+    g = _ref_linear(A, Wg).bfloat16().float()
+    u = _ref_linear(A, Wu).bfloat16().float()
+    ref = (torch.nn.functional.gelu(g, approximate="tanh").bfloat16().float() * u).bfloat16().float()
+    assert (out.float() - ref).abs().max().item() <= 3e-2 * max(1.0, ref.abs().max().item())
+
+
+def test_gemm_tc_throughput_report(cuda):
+    """Not an assertion on speed: prints achieved TFLOP/s of the tcgen05 kernel for the log."""
+    M, N, K = 8192, 8192, 2048
+    A = _rand((M, K), cuda, seed=15)
+    W = _rand((N, K), cuda, 0.02, seed=16)
+    out = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    for bn in (128, 256):
+        for _ in range(3):
+            pb.gemm(A, W, out, bn=bn)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            pb.gemm(A, W, out, bn=bn)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        print(f"\n[tc gemm] M={M} N={N} K={K} bn={bn}: {ms:.3f} ms  {2.0 * M * N * K / ms / 1e9:.1f} TFLOP/s")
+    ref = _ref_linear(A[:256], W[:256])
+    assert (out[:256, :256].float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item() + 1e-3
