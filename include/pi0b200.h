@@ -48,7 +48,8 @@ typedef struct pi0_model_cfg {
   int32_t n_siglip_layers;/* <= PI0_SIGLIP_LAYERS (27 in the shipped model; fewer in depth-reduced tests) */
   int32_t n_gemma_layers; /* <= PI0_GEMMA_LAYERS, shared by Gemma-2B and the action expert (18)     */
   int32_t images_pre_normalized; /* 1 = skip prepare_images' img*2-1                 */
-  int32_t reserved[2];
+  int32_t n_euler_iters;  /* iterations of `while time >= -dt/2` with fp32-accumulated time (0 = num_steps) */
+  int32_t reserved;
 } pi0_model_cfg;
 
 /* ---- weights: packed by the host loader (int-act_b200/weights.py) into device tensors ----------

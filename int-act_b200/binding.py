@@ -24,7 +24,7 @@ class ModelCfg(C.Structure):
         ("max_state_dim", C.c_int32), ("max_action_dim", C.c_int32), ("num_steps", C.c_int32),
         ("dtype", C.c_int32), ("gemm_impl", C.c_int32), ("max_batch", C.c_int32), ("num_sms", C.c_int32),
         ("skip_dead_work", C.c_int32), ("n_siglip_layers", C.c_int32), ("n_gemma_layers", C.c_int32),
-        ("images_pre_normalized", C.c_int32), ("reserved", C.c_int32 * 2),
+        ("images_pre_normalized", C.c_int32), ("n_euler_iters", C.c_int32), ("reserved", C.c_int32),
     ]
 
 

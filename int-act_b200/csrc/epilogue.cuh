@@ -176,6 +176,7 @@ __device__ __forceinline__ void epi_rope_chunk(const EpiParams& ep, int row, int
   float o1[32], o2[32];
   if (which < 2) {
     int pos = ep.pos_ids[row];
+    if (pos < 0) pos = 0;  // leading pad tokens have cumsum(pad)-1 == -1; their K/V are never attended
     const float* cs = ep.rope_cos + (int64_t)pos * 128 + c * 32;
     const float* sn = ep.rope_sin + (int64_t)pos * 128 + c * 32;
 #pragma unroll

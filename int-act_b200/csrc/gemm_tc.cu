@@ -271,7 +271,11 @@ static int launch_cfg(const GemmProblem& g, int num_sms, cudaStream_t stream) {
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
-  PI0_REQUIRE(g.N % 8 == 0 || g.epi_mode == EPI_EULER || g.epi.vt != nullptr, "gemm_tc: N=%d must be a multiple of 8", g.N);
+  // a ragged N is fine for EPI_STORE when nothing is read per column and the row pitch covers the 8-wide store
+  const bool ragged_ok = g.epi_mode == EPI_STORE && g.epi.bias == nullptr && g.epi.res == nullptr &&
+                         g.epi.ldc >= (int64_t)((g.N + 7) / 8) * 8;
+  PI0_REQUIRE(g.N % 8 == 0 || g.epi_mode == EPI_EULER || g.epi.vt != nullptr || ragged_ok,
+              "gemm_tc: N=%d must be a multiple of 8", g.N);
   switch (g.epi_mode) {
     case EPI_STORE:
       switch (g.bn) {

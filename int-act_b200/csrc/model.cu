@@ -1,15 +1,515 @@
-// placeholder until the model orchestration lands (next commit)
+// Host orchestration of the Pi0 `sample_actions` path behind the C ABI: SigLIP -> prefix embedding ->
+// Gemma-2B prefill (KV cache written in place by the QKV GEMM epilogue) -> 10-step flow-matching Euler
+// loop of the action expert over the cached prefix. No device allocation, no synchronisation: every
+// buffer is carved from the caller's workspace and every launch goes to the caller's stream, so
+// pi0_infer / pi0_denoise_loop are CUDA-graph capturable.
+//
+// Reference arithmetic followed ([mirror] = /root/reference/src/model/mvla/*):
+//   embed_prefix        modeling_mvla.py:582-624,636-641      embed_image      mllm.py:182-187
+//   Gemma layer body    mllm.py:206-245                        attention        mllm.py:265-317
+//   embed_suffix        modeling_mvla.py:643-694               denoise_step     modeling_mvla.py:806-839
+//   Euler loop          modeling_mvla.py:787-803
+#include <cstring>
+#include <new>
+
 #include "../../include/pi0b200.h"
-#include "common.cuh"
+#include "elementwise.cuh"
+
 using namespace pi0;
-extern "C" {
-size_t pi0_workspace_bytes(const pi0_model_cfg*) { return 0; }
-int pi0_ctx_create(const pi0_model_cfg*, const pi0_weights*, void*, size_t, pi0_ctx**) { set_error("not implemented"); return -3; }
-void pi0_ctx_destroy(pi0_ctx*) {}
-int pi0_siglip_forward(pi0_ctx*, int, int, const float*, float, float, void*) { set_error("not implemented"); return -3; }
-int pi0_embed_language(pi0_ctx*, int, const int64_t*, void*) { set_error("not implemented"); return -3; }
-int pi0_prefill(pi0_ctx*, int, const uint8_t*, const uint8_t*, void*) { set_error("not implemented"); return -3; }
-int pi0_denoise_loop(pi0_ctx*, int, const float*, float*, void*) { set_error("not implemented"); return -3; }
-int pi0_infer(pi0_ctx*, int, const float* const*, float, float, const uint8_t*, const int64_t*, const uint8_t*, const float*, float*, void*) { set_error("not implemented"); return -3; }
-const void* pi0_debug_buffer(pi0_ctx*, const char*, int64_t*) { return nullptr; }
+
+namespace {
+
+constexpr int kPatches = 256;
+constexpr int kVisHidden = 1152, kVisInter = 4304, kVisHeads = 16, kVisHd = 72, kPatchK = 592;
+constexpr int kHidden = 2048, kInter = 16384, kExpHidden = 1024, kExpInter = 4096;
+constexpr int kHeads = 8, kHd = 256, kProjW = 1024;
+constexpr float kEps = 1e-6f;
+
+inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+struct Buf {
+  const char* name;
+  size_t offset;
+  size_t bytes;
+};
+
+}  // namespace
+
+struct pi0_ctx {
+  pi0_model_cfg cfg;
+  pi0_weights w;
+  uint8_t* base;
+  size_t ws_bytes;
+  int es;  // element size of the activation type
+  int P, S, H, L, ncam, maxB;
+  int kv_pitch;   // rows per sample in the K cache (P + S)
+  int sc_pitch;   // score row pitch (>= P + S, multiple of 8)
+  int vt_pitch;   // V^T row pitch (>= P + S, multiple of 8)
+  // SigLIP
+  void *col, *xs, *hs, *qk_s, *vt_s, *sc_s, *att_s, *mlp_s;
+  // Gemma prefill
+  void *xp, *hp, *qp, *sc_p, *att_p, *act_p;
+  void *kcache, *vtcache;  // [layers][B][kv_pitch][256], [layers][B][256][vt_pitch]
+  // expert
+  void *suf, *xe, *ye, *he, *qe, *sc_e, *att_e, *act_e, *xt_act, *st_act, *a1, *a2, *hfin;
+  uint8_t* pad;
+  int *prefix_pos, *suffix_pos, *suffix_cum;
+  Buf bufs[40];
+  int nbufs;
+};
+
+namespace {
+
+// ---- workspace carving (shared by pi0_workspace_bytes and pi0_ctx_create) ------------------------------
+struct Carver {
+  size_t off = 0;
+  uint8_t* base = nullptr;
+  pi0_ctx* ctx = nullptr;
+  void* take(const char* name, size_t bytes) {
+    size_t o = off;
+    off = round_up((int64_t)(off + bytes), 1024);
+    if (ctx && ctx->nbufs < 40) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
+    return base ? base + o : nullptr;
+  }
+};
+
+int validate_cfg(const pi0_model_cfg* c) {
+  PI0_REQUIRE(c != nullptr, "null cfg");
+  PI0_REQUIRE(c->n_cams >= 1 && c->n_cams <= 4, "n_cams=%d out of range [1,4]", c->n_cams);
+  PI0_REQUIRE(c->lang_len >= 1 && c->lang_len <= 1024 && c->lang_len % 8 == 0,
+              "lang_len=%d must be a positive multiple of 8", c->lang_len);
+  PI0_REQUIRE(c->horizon >= 1 && c->horizon <= 64, "horizon=%d out of range [1,64]", c->horizon);
+  PI0_REQUIRE(c->max_state_dim == 32 && c->max_action_dim == 32, "max_state_dim/max_action_dim must be 32");
+  PI0_REQUIRE(c->num_steps >= 1 && c->num_steps <= 100, "num_steps=%d out of range", c->num_steps);
+  PI0_REQUIRE(c->dtype == 0 || c->dtype == 1, "dtype=%d must be 0 (bf16) or 1 (fp32)", c->dtype);
+  PI0_REQUIRE(c->max_batch >= 1, "max_batch=%d must be >= 1", c->max_batch);
+  PI0_REQUIRE(c->n_siglip_layers >= 0 && c->n_siglip_layers <= PI0_SIGLIP_LAYERS, "n_siglip_layers=%d",
+              c->n_siglip_layers);
+  PI0_REQUIRE(c->n_gemma_layers >= 1 && c->n_gemma_layers <= PI0_GEMMA_LAYERS, "n_gemma_layers=%d",
+              c->n_gemma_layers);
+  return 0;
 }
+
+void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
+  const size_t es = cfg.dtype == 1 ? 4 : 2;
+  const int64_t B = cfg.max_batch;
+  const int P = cfg.n_cams * kPatches + cfg.lang_len, S = 1 + cfg.horizon, H = cfg.horizon;
+  const int kvp = P + S;
+  const int scp = (int)round_up(kvp, 8), vtp = (int)round_up(kvp, 8);
+  const int NL = cfg.n_gemma_layers;
+  const int64_t Ms = B * kPatches, Mg = B * P, Me = B * S;
+  pi0_ctx dummy;
+  pi0_ctx& x = c ? *c : dummy;
+  x.col = cv.take("siglip.col", Ms * kPatchK * es);
+  x.xs = cv.take("siglip.x", Ms * kVisHidden * es);
+  x.hs = cv.take("siglip.h", Ms * kVisHidden * es);
+  x.qk_s = cv.take("siglip.qk", Ms * 2 * kVisHidden * es);
+  x.vt_s = cv.take("siglip.vt", B * kVisHeads * kVisHd * kPatches * es);
+  x.sc_s = cv.take("siglip.scores", B * kVisHeads * kPatches * kPatches * es);
+  x.att_s = cv.take("siglip.att", Ms * kVisHidden * es);
+  x.mlp_s = cv.take("siglip.mlp", Ms * kVisInter * es);
+  x.xp = cv.take("prefix.x", Mg * kHidden * es);
+  x.hp = cv.take("prefix.h", Mg * kHidden * es);
+  x.qp = cv.take("prefix.q", Mg * kHidden * es);
+  x.sc_p = cv.take("prefix.scores", B * P * kHeads * scp * es);
+  x.att_p = cv.take("prefix.att", Mg * kHidden * es);
+  x.act_p = cv.take("prefix.act", Mg * kInter * es);
+  x.kcache = cv.take("kcache", (int64_t)NL * B * kvp * kHd * es);
+  x.vtcache = cv.take("vtcache", (int64_t)NL * B * kHd * vtp * es);
+  x.suf = cv.take("suffix.embs", Me * kExpHidden * es);
+  x.xe = cv.take("suffix.x", Me * kExpHidden * es);
+  x.ye = cv.take("suffix.y", Me * kExpHidden * es);
+  x.he = cv.take("suffix.h", Me * kExpHidden * es);
+  x.qe = cv.take("suffix.q", Me * kHidden * es);
+  x.sc_e = cv.take("suffix.scores", B * S * kHeads * scp * es);
+  x.att_e = cv.take("suffix.att", Me * kHidden * es);
+  x.act_e = cv.take("suffix.act", Me * kExpInter * es);
+  x.xt_act = cv.take("suffix.xt", B * H * 32 * es);
+  x.st_act = cv.take("suffix.state", B * 32 * es);
+  x.a1 = cv.take("suffix.a1", B * H * kProjW * es);
+  x.a2 = cv.take("suffix.a2", B * H * kProjW * es);
+  x.hfin = cv.take("suffix.hfin", B * H * kExpHidden * es);
+  x.pad = (uint8_t*)cv.take("pad", B * P);
+  x.prefix_pos = (int*)cv.take("prefix_pos", B * P * 4);
+  x.suffix_pos = (int*)cv.take("suffix_pos", B * S * 4);
+  x.suffix_cum = (int*)cv.take("suffix_cum", S * 4);
+  if (c) {
+    c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
+    c->kv_pitch = kvp; c->sc_pitch = scp; c->vt_pitch = vtp; c->es = (int)es;
+  }
+}
+
+__global__ void suffix_cum_kernel(int* cum, int S) {
+  // att_masks of the suffix = [1, 1, 0, ...] (modeling_mvla.py:686-692) => cumsum = [1, 2, 2, ...]
+  for (int i = threadIdx.x; i < S; i += blockDim.x) cum[i] = i == 0 ? 1 : 2;
+}
+
+inline void* at(void* p, int64_t elems, int es) { return (uint8_t*)p + elems * es; }
+inline const void* at(const void* p, int64_t elems, int es) { return (const uint8_t*)p + elems * es; }
+
+int run_gemm(pi0_ctx* c, const GemmProblem& g, cudaStream_t s) {
+  return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s);
+}
+
+int run_rmsnorm(pi0_ctx* c, const void* x, void* y, const float* g, int M, int D, int rpb_in, int rpb_out, int off,
+                cudaStream_t s) {
+  if (c->cfg.dtype == 1) return rmsnorm<float>((const float*)x, (float*)y, g, M, D, kEps, rpb_in, rpb_out, off, s);
+  return rmsnorm<bf16>((const bf16*)x, (bf16*)y, g, M, D, kEps, rpb_in, rpb_out, off, s);
+}
+int run_layernorm(pi0_ctx* c, const void* x, void* y, const float* w, const float* b, int M, int D, cudaStream_t s) {
+  if (c->cfg.dtype == 1) return layernorm<float>((const float*)x, (float*)y, w, b, M, D, kEps, s);
+  return layernorm<bf16>((const bf16*)x, (bf16*)y, w, b, M, D, kEps, s);
+}
+int run_softmax(pi0_ctx* c, void* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
+                const uint8_t* pad, int pad_pitch, const int* cum, int heads, cudaStream_t s) {
+  if (c->cfg.dtype == 1)
+    return softmax_rows<float>((float*)sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads,
+                               s);
+  return softmax_rows<bf16>((bf16*)sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads, s);
+}
+int run_cast(pi0_ctx* c, const float* in, void* out, int64_t n, cudaStream_t s) {
+  if (c->cfg.dtype == 1) return cast_f32<float>(in, (float*)out, n, s);
+  return cast_f32<bf16>(in, (bf16*)out, n, s);
+}
+
+// pick the N tile of the tcgen05 kernel so that the tile count fills the SMs reasonably
+int pick_bn(int M, int N) {
+  const int tm = (M + 127) / 128;
+  if (N % 256 == 0 && (int64_t)tm * (N / 256) >= 148) return 256;
+  if ((int64_t)tm * ((N + 127) / 128) >= 148) return 128;
+  if ((int64_t)tm * ((N + 63) / 64) >= 120) return 64;
+  return N >= 64 ? (tm * ((N + 63) / 64) >= 64 ? 64 : 32) : 32;
+}
+
+// ---- one Gemma-style layer (prefill when suffix == false, expert over the cached prefix otherwise) ----
+struct LayerIO {
+  const void* x_in;  // residual stream in  [M, hidden]
+  void* y;           // after attention     [M, hidden]
+  void* x_out;       // after MLP           [M, hidden]
+};
+
+int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bool kv_only, cudaStream_t s) {
+  const int es = c->es;
+  const int T = suffix ? c->S : c->P;            // tokens per sample in this pass
+  const int M = B * T;
+  const int hidden = suffix ? kExpHidden : kHidden;
+  const int inter = suffix ? kExpInter : kInter;
+  const pi0_gemma_layer_w& w = suffix ? c->w.exp[layer] : c->w.gem[layer];
+  void* h = suffix ? c->he : c->hp;
+  void* q = suffix ? c->qe : c->qp;
+  void* sc = suffix ? c->sc_e : c->sc_p;
+  void* att = suffix ? c->att_e : c->att_p;
+  void* act = suffix ? c->act_e : c->act_p;
+  const int toff = suffix ? c->P : 0;
+  const int n_keys = suffix ? c->P + c->S : c->P;
+  void* kc = at(c->kcache, (int64_t)layer * c->maxB * c->kv_pitch * kHd, es);
+  void* vt = at(c->vtcache, (int64_t)layer * c->maxB * kHd * c->vt_pitch, es);
+
+  // input RMSNorm
+  PI0_TRY(run_rmsnorm(c, io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
+
+  // fused QKV + RoPE; K and V^T land in the cache (mllm.py:216-221 + fill_kv_cache)
+  {
+    GemmProblem g = gemm_problem(h, hidden, w.wqkv, hidden, M, (kHeads + 2) * kHd, hidden);
+    g.epi_mode = EPI_ROPE; g.bn = 256;
+    g.epi.out = q; g.epi.ldc = kHidden;
+    g.epi.rope_cos = c->w.rope_cos; g.epi.rope_sin = c->w.rope_sin;
+    g.epi.pos_ids = suffix ? c->suffix_pos : c->prefix_pos;
+    g.epi.kcache = kc; g.epi.kv_pitch = c->kv_pitch; g.epi.n_q_heads = kHeads;
+    g.epi.vt = vt; g.epi.vt_pitch = c->vt_pitch; g.epi.vt_rpb = T; g.epi.vt_toff = toff;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  if (kv_only) return 0;
+
+  // scores[b, t*8+h, j] = rnd(rnd(q . k) * 256^-0.5)   (MQA: the 8 heads of a token are 8 rows against one K)
+  {
+    GemmProblem g = gemm_problem(q, kHd, kc, kHd, T * kHeads, n_keys, kHd);
+    g.nz0 = B; g.a_z0 = (int64_t)T * kHeads * kHd; g.w_z0 = (int64_t)c->kv_pitch * kHd;
+    g.bn = n_keys > 256 ? 128 : 64;
+    g.epi.out = sc; g.epi.ldc = c->sc_pitch; g.epi.out_z0 = (int64_t)T * kHeads * c->sc_pitch;
+    g.epi.alpha = 0.0625f;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  // masked softmax (mllm.py:299-307); prefix keys gated by pad, suffix keys by the block-causal cumsum rule
+  PI0_TRY(run_softmax(c, sc, (int64_t)B * T * kHeads, T * kHeads, c->sc_pitch, n_keys, c->P, c->pad, c->P,
+                      suffix ? c->suffix_cum : nullptr, kHeads, s));
+  // att[b, t*8+h, :] = probs . V   (V^T is the K-major operand)
+  {
+    GemmProblem g = gemm_problem(sc, c->sc_pitch, vt, c->vt_pitch, T * kHeads, kHd, n_keys);
+    g.nz0 = B; g.a_z0 = (int64_t)T * kHeads * c->sc_pitch; g.w_z0 = (int64_t)kHd * c->vt_pitch;
+    g.bn = 256;
+    g.epi.out = att; g.epi.ldc = kHd; g.epi.out_z0 = (int64_t)T * kHeads * kHd;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  // o_proj + residual
+  {
+    GemmProblem g = gemm_problem(att, kHidden, w.wo, kHidden, M, hidden, kHidden);
+    g.bn = pick_bn(M, hidden);
+    g.epi.out = io.y; g.epi.ldc = hidden; g.epi.res = io.x_in; g.epi.ldr = hidden;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  PI0_TRY(run_rmsnorm(c, io.y, h, w.g2, M, hidden, 0, 0, 0, s));
+  // GeGLU: gate/up interleaved per 256-row tile at pack time
+  {
+    GemmProblem g = gemm_problem(h, hidden, w.wgu, hidden, M, 2 * inter, hidden);
+    g.epi_mode = EPI_GEGLU; g.bn = 256;
+    g.epi.out = act; g.epi.ldc = inter;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  {
+    GemmProblem g = gemm_problem(act, inter, w.wdown, inter, M, hidden, inter);
+    g.bn = pick_bn(M, hidden);
+    g.epi.out = io.x_out; g.epi.ldc = hidden; g.epi.res = io.y; g.epi.ldr = hidden;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  return 0;
+}
+
+int check_batch(pi0_ctx* c, int B) {
+  PI0_REQUIRE(c != nullptr, "null ctx");
+  PI0_REQUIRE(B >= 1 && B <= c->maxB, "batch %d outside [1, max_batch=%d]", B, c->maxB);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t pi0_workspace_bytes(const pi0_model_cfg* cfg) {
+  if (validate_cfg(cfg) != 0) return 0;
+  Carver cv;
+  carve(cv, nullptr, *cfg);
+  return cv.off + 1024;
+}
+
+int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspace, size_t workspace_bytes,
+                   pi0_ctx** out) {
+  PI0_TRY(validate_cfg(cfg));
+  PI0_REQUIRE(w != nullptr && workspace != nullptr && out != nullptr, "pi0_ctx_create: null argument");
+  const size_t need = pi0_workspace_bytes(cfg);
+  PI0_REQUIRE(workspace_bytes >= need, "workspace too small: %zu < %zu bytes", workspace_bytes, need);
+  PI0_REQUIRE(w->max_pos >= cfg->n_cams * kPatches + cfg->lang_len + 1 + cfg->horizon,
+              "rope table covers %d positions, need %d", w->max_pos,
+              cfg->n_cams * kPatches + cfg->lang_len + 1 + cfg->horizon);
+  pi0_ctx* c = new (std::nothrow) pi0_ctx();
+  PI0_REQUIRE(c != nullptr, "out of host memory");
+  c->cfg = *cfg;
+  c->w = *w;
+  c->nbufs = 0;
+  uintptr_t b = ((uintptr_t)workspace + 1023) & ~(uintptr_t)1023;
+  c->base = (uint8_t*)b;
+  c->ws_bytes = workspace_bytes;
+  Carver cv;
+  cv.base = c->base;
+  cv.ctx = c;
+  carve(cv, c, *cfg);
+  *out = c;
+  return 0;
+}
+
+void pi0_ctx_destroy(pi0_ctx* ctx) { delete ctx; }
+
+const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems) {
+  if (!ctx || !name) return nullptr;
+  for (int i = 0; i < ctx->nbufs; ++i) {
+    if (strcmp(ctx->bufs[i].name, name) == 0) {
+      const bool raw = strcmp(name, "pad") == 0 || strcmp(name, "prefix_pos") == 0 ||
+                       strcmp(name, "suffix_pos") == 0 || strcmp(name, "suffix_cum") == 0;
+      const size_t unit = strcmp(name, "pad") == 0 ? 1 : (raw ? 4 : (size_t)ctx->es);
+      if (n_elems) *n_elems = (int64_t)(ctx->bufs[i].bytes / unit);
+      return ctx->base + ctx->bufs[i].offset;
+    }
+  }
+  return nullptr;
+}
+
+int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float scale, float shift, void* stream) {
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(cam >= 0 && cam < c->ncam, "camera index %d outside [0,%d)", cam, c->ncam);
+  PI0_REQUIRE(images != nullptr, "null images");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int es = c->es;
+  const int M = B * kPatches;
+  const pi0_weights& w = c->w;
+
+  // patch embedding as a GEMM over the fused im2col / normalise (modeling_mvla.py:366-367 + Conv2d k14 s14),
+  // bias and position embedding in the epilogue
+  if (c->cfg.dtype == 1) PI0_TRY(im2col_patch<float>(images, (float*)c->col, B, kPatchK, scale, shift, s));
+  else PI0_TRY(im2col_patch<bf16>(images, (bf16*)c->col, B, kPatchK, scale, shift, s));
+  {
+    GemmProblem g = gemm_problem(c->col, kPatchK, w.patch_w, kPatchK, M, kVisHidden, kPatchK);
+    g.bn = pick_bn(M, kVisHidden);
+    g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = w.patch_b;
+    g.epi.res = w.pos_emb; g.epi.ldr = kVisHidden; g.epi.res_row_mod = kPatches;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  const int64_t qk_ld = 2 * kVisHidden;
+  for (int l = 0; l < c->cfg.n_siglip_layers; ++l) {
+    const pi0_siglip_layer_w& lw = w.sig[l];
+    PI0_TRY(run_layernorm(c, c->xs, c->hs, lw.ln1_w, lw.ln1_b, M, kVisHidden, s));
+    {  // fused q|k|v projection; the V columns are written transposed per head for the P.V GEMM
+      GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wqkv, kVisHidden, M, 3 * kVisHidden, kVisHidden);
+      g.bn = pick_bn(M, 3 * kVisHidden);
+      g.epi.out = c->qk_s; g.epi.ldc = qk_ld; g.epi.bias = lw.bqkv;
+      g.epi.vt = c->vt_s; g.epi.vt_col0 = 2 * kVisHidden; g.epi.vt_hd = kVisHd; g.epi.vt_heads = kVisHeads;
+      g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    {  // scores[b,h] = rnd(rnd(q k^T) * 72^-0.5), bidirectional
+      GemmProblem g = gemm_problem(c->qk_s, qk_ld, at(c->qk_s, kVisHidden, es), qk_ld, kPatches, kPatches, kVisHd);
+      g.nz0 = kVisHeads; g.nz1 = B;
+      g.a_z0 = kVisHd; g.a_z1 = (int64_t)kPatches * qk_ld; g.w_z0 = kVisHd; g.w_z1 = (int64_t)kPatches * qk_ld;
+      g.bn = 128;
+      g.epi.out = c->sc_s; g.epi.ldc = kPatches; g.epi.out_z0 = (int64_t)kPatches * kPatches;
+      g.epi.out_z1 = (int64_t)kVisHeads * kPatches * kPatches;
+      g.epi.alpha = 0.11785113019775793f;  // 72 ** -0.5
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    PI0_TRY(run_softmax(c, c->sc_s, (int64_t)B * kVisHeads * kPatches, kVisHeads * kPatches, kPatches, kPatches,
+                        kPatches, nullptr, 0, nullptr, 1, s));
+    {  // att[b, t, h*72 + d] = probs[b,h] . V[b,h]
+      GemmProblem g = gemm_problem(c->sc_s, kPatches, c->vt_s, kPatches, kPatches, kVisHd, kPatches);
+      g.nz0 = kVisHeads; g.nz1 = B;
+      g.a_z0 = (int64_t)kPatches * kPatches; g.a_z1 = (int64_t)kVisHeads * kPatches * kPatches;
+      g.w_z0 = (int64_t)kVisHd * kPatches; g.w_z1 = (int64_t)kVisHeads * kVisHd * kPatches;
+      g.bn = 128;
+      g.epi.out = c->att_s; g.epi.ldc = kVisHidden; g.epi.out_z0 = kVisHd;
+      g.epi.out_z1 = (int64_t)kPatches * kVisHidden;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    {  // out_proj + residual (in place on the residual stream: each element is read then written by one thread)
+      GemmProblem g = gemm_problem(c->att_s, kVisHidden, lw.wo, kVisHidden, M, kVisHidden, kVisHidden);
+      g.bn = pick_bn(M, kVisHidden);
+      g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bo; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    PI0_TRY(run_layernorm(c, c->xs, c->hs, lw.ln2_w, lw.ln2_b, M, kVisHidden, s));
+    {
+      GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wfc1, kVisHidden, M, kVisInter, kVisHidden);
+      g.bn = pick_bn(M, kVisInter);
+      g.epi.out = c->mlp_s; g.epi.ldc = kVisInter; g.epi.bias = lw.bfc1; g.epi.act = ACT_GELU_TANH;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    {
+      GemmProblem g = gemm_problem(c->mlp_s, kVisInter, lw.wfc2, kVisInter, M, kVisHidden, kVisInter);
+      g.bn = pick_bn(M, kVisHidden);
+      g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bfc2; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+  }
+  PI0_TRY(run_layernorm(c, c->xs, c->hs, w.post_ln_w, w.post_ln_b, M, kVisHidden, s));
+  {  // projector, "/ sqrt(2048)" of HF get_image_features and "* sqrt(2048)" of embed_prefix, written into the
+     // prefix rows [b*P + cam*256, +256)
+    GemmProblem g = gemm_problem(c->hs, kVisHidden, w.proj_w, kVisHidden, M, kHidden, kVisHidden);
+    g.bn = pick_bn(M, kHidden);
+    g.epi.out = c->xp; g.epi.ldc = kHidden; g.epi.bias = w.proj_b;
+    g.epi.post_div = 45.254833995939045f;                    // sqrt(2048) in fp32
+    g.epi.post_mul = c->cfg.dtype == 1 ? 45.254833995939045f : 45.25f;  // sqrt(2048) as a 0-dim tensor of the act dtype
+    g.epi.rpb_in = kPatches; g.epi.rpb_out = c->P; g.epi.row_off = cam * kPatches;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  return 0;
+}
+
+int pi0_embed_language(pi0_ctx* c, int B, const int64_t* tokens, void* stream) {
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(tokens != nullptr, "null tokens");
+  cudaStream_t s = (cudaStream_t)stream;
+  const float scale = 45.254833995939045f;
+  if (c->cfg.dtype == 1)
+    return embed_tokens<float>(tokens, (const float*)c->w.embed, (float*)c->xp, B, c->L, c->P, c->ncam * kPatches,
+                               kHidden, c->w.vocab, scale, s);
+  return embed_tokens<bf16>(tokens, (const bf16*)c->w.embed, (bf16*)c->xp, B, c->L, c->P, c->ncam * kPatches, kHidden,
+                            c->w.vocab, scale, s);
+}
+
+int pi0_prefill(pi0_ctx* c, int B, const uint8_t* img_masks, const uint8_t* lang_masks, void* stream) {
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(img_masks != nullptr && lang_masks != nullptr, "null masks");
+  cudaStream_t s = (cudaStream_t)stream;
+  PI0_TRY(build_pad(img_masks, lang_masks, c->pad, B, c->ncam, c->L, s));
+  PI0_TRY(position_ids(c->pad, B, c->P, c->S, c->prefix_pos, c->suffix_pos, s));
+  suffix_cum_kernel<<<1, 64, 0, s>>>(c->suffix_cum, c->S);
+  PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  const int NL = c->cfg.n_gemma_layers;
+  for (int l = 0; l < NL; ++l) {
+    // the prefill output is discarded by sample_actions (modeling_mvla.py:776): the last layer only contributes K/V
+    const bool kv_only = c->cfg.skip_dead_work != 0 && l == NL - 1;
+    // the residual stream is updated in place (each epilogue thread reads then writes its own elements)
+    LayerIO io{c->xp, c->xp, c->xp};
+    PI0_TRY(gemma_layer(c, B, l, false, io, kv_only, s));
+  }
+  return 0;
+}
+
+int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* stream) {
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(state != nullptr && x_t != nullptr, "null state / x_t");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int H = c->H, S = c->S;
+  const pi0_weights& w = c->w;
+  const float dt = -1.0f / (float)c->cfg.num_steps;
+
+  // state_proj -> suffix row 0 of every sample (input-independent across steps)
+  PI0_TRY(run_cast(c, state, c->st_act, (int64_t)B * 32, s));
+  {
+    GemmProblem g = gemm_problem(c->st_act, 32, w.state_w, 32, B, kExpHidden, 32);
+    g.bn = 32;
+    g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.state_b;
+    g.epi.rpb_in = 1; g.epi.rpb_out = S; g.epi.row_off = 0;
+    PI0_TRY(run_gemm(c, g, s));
+  }
+  const int n_iters = c->cfg.n_euler_iters > 0 ? c->cfg.n_euler_iters : c->cfg.num_steps;
+  for (int step = 0; step < n_iters; ++step) {
+    // embed_suffix: action_in_proj -> (time half folded into the bias) mlp_in -> SiLU -> mlp_out -> suffix rows 1..H
+    PI0_TRY(run_cast(c, x_t, c->xt_act, (int64_t)B * H * 32, s));
+    {
+      GemmProblem g = gemm_problem(c->xt_act, 32, w.action_in_w, 32, B * H, kProjW, 32);
+      g.bn = 32;
+      g.epi.out = c->a1; g.epi.ldc = kProjW; g.epi.bias = w.action_in_b;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    {
+      GemmProblem g = gemm_problem(c->a1, kProjW, w.time_in_wa, kProjW, B * H, kProjW, kProjW);
+      g.bn = 32;
+      g.epi.out = c->a2; g.epi.ldc = kProjW; g.epi.bias = w.time_bias + (int64_t)step * kProjW;
+      g.epi.act = ACT_SILU;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    {
+      GemmProblem g = gemm_problem(c->a2, kProjW, w.time_out_w, kProjW, B * H, kExpHidden, kProjW);
+      g.bn = 32;
+      g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.time_out_b;
+      g.epi.rpb_in = H; g.epi.rpb_out = S; g.epi.row_off = 1;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+    for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
+      LayerIO io{l == 0 ? c->suf : c->xe, c->ye, c->xe};
+      PI0_TRY(gemma_layer(c, B, l, true, io, false, s));
+    }
+    // final norm on the last H rows of every sample, action_out_proj and the Euler update x_t += dt * v_t
+    PI0_TRY(run_rmsnorm(c, c->xe, c->hfin, w.exp_norm_g, B * H, kExpHidden, H, S, 1, s));
+    {
+      GemmProblem g = gemm_problem(c->hfin, kExpHidden, w.action_out_w, kExpHidden, B * H, 32, kExpHidden);
+      g.epi_mode = EPI_EULER; g.bn = 32;
+      g.epi.out = x_t; g.epi.ldc = 32; g.epi.bias = w.action_out_b; g.epi.dt = dt;
+      PI0_TRY(run_gemm(c, g, s));
+    }
+  }
+  return 0;
+}
+
+int pi0_infer(pi0_ctx* c, int B, const float* const* images, float img_scale, float img_shift,
+              const uint8_t* img_masks, const int64_t* tokens, const uint8_t* lang_masks, const float* state,
+              float* x_t, void* stream) {
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(images != nullptr, "null images");
+  for (int cam = 0; cam < c->ncam; ++cam)
+    PI0_TRY(pi0_siglip_forward(c, B, cam, images[cam], img_scale, img_shift, stream));
+  PI0_TRY(pi0_embed_language(c, B, tokens, stream));
+  PI0_TRY(pi0_prefill(c, B, img_masks, lang_masks, stream));
+  return pi0_denoise_loop(c, B, state, x_t, stream);
+}
+
+}  // extern "C"

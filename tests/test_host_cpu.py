@@ -1,0 +1,123 @@
+"""CPU: host logic of the product package (config contract, weight packing, policy queue, C-ABI symbols)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from int_act_b200 import binding as pb
+from int_act_b200 import weights as W
+from int_act_b200.config import PI0Config, bridge_config, libero_config, load_yaml
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+# the reference's shipped model config (config/models/pi0_finetune_bridge.json), restated key for key
+BRIDGE_JSON = {
+    "type": "pi0", "n_obs_steps": 1, "device": "cpu", "use_amp": True,
+    "normalization_mapping": {"VISUAL": "IDENTITY", "STATE": "IDENTITY", "ACTION": "IDENTITY"},
+    "input_features": {"observation.images.top": {"shape": [3, 224, 224], "type": "VISUAL"},
+                       "observation.state": {"shape": [7], "type": "STATE"}},
+    "output_features": {"action": {"type": "ACTION", "shape": [7]}},
+    "chunk_size": 4, "n_action_steps": 4, "max_state_dim": 32, "max_action_dim": 32,
+    "resize_imgs_with_padding": [224, 224], "empty_cameras": 0, "adapt_to_pi_aloha": False,
+    "use_delta_joint_actions_aloha": False, "tokenizer_max_length": 72, "proj_width": 1024, "num_steps": 10,
+    "use_cache": True, "attention_implementation": "eager", "freeze_vision_encoder": False,
+    "train_expert_only": False, "train_state_proj": True, "paligemma_pretrained_path": None,
+    "optimizer_lr": 5e-5, "optimizer_betas": [0.9, 0.999], "optimizer_eps": 1e-8, "optimizer_weight_decay": 0,
+    "scheduler_warmup_steps": 200, "scheduler_decay_steps": 30000, "scheduler_decay_lr": 2.5e-06,
+}
+
+
+def test_config_accepts_reference_keys_and_validates():
+    cfg = PI0Config.from_dict(BRIDGE_JSON)
+    assert cfg.n_cams == 1 and cfg.tokenizer_max_length == 72 and cfg.n_action_steps == 4
+    assert cfg.action_feature.shape == (7,) and cfg.robot_state_feature.shape == (7,)
+    assert cfg.extra["optimizer_lr"] == 5e-5 and cfg.resize_imgs_with_padding == (224, 224)
+    assert PI0Config.from_dict(cfg.to_dict()).to_dict() == cfg.to_dict()
+    assert bridge_config().to_dict()["input_features"] == cfg.to_dict()["input_features"]
+    assert libero_config().n_cams == 2
+    with pytest.raises(ValueError):
+        PI0Config.from_dict({**BRIDGE_JSON, "n_action_steps": 8})
+    with pytest.raises(ValueError):
+        PI0Config.from_dict({**BRIDGE_JSON, "n_obs_steps": 2})
+    with pytest.raises(NotImplementedError):
+        PI0Config.from_dict({**BRIDGE_JSON, "use_delta_joint_actions_aloha": True})
+
+
+def test_yaml_include(tmp_path):
+    import json
+
+    (tmp_path / "models").mkdir()
+    (tmp_path / "models" / "m.json").write_text(json.dumps(BRIDGE_JSON))
+    (tmp_path / "exp.yaml").write_text("seed: 42\nmodel_cfg: !include models/m.json\neval_cfg:\n  port: 8000\n")
+    y = load_yaml(str(tmp_path / "exp.yaml"))
+    assert y["seed"] == 42 and y["model_cfg"]["tokenizer_max_length"] == 72 and y["eval_cfg"]["port"] == 8000
+    assert PI0Config.from_dict(y["model_cfg"]).num_steps == 10
+
+
+def test_state_dict_layout_and_param_counts():
+    shapes = W.state_dict_shapes(W.Dims())
+    n = lambda pref: sum(int(torch.tensor(s).prod()) for k, s in shapes.items() if k.startswith(pref))
+    assert n(W.VT) + n(W.PROJ) == 414_441_856 - 0 or abs(n(W.VT) + n(W.PROJ) - 414.4e6) < 0.5e6  # SigLIP + projector
+    gem = n(W.LM) - 257152 * 2048
+    assert abs(gem - 1981.8e6) < 0.5e6          # 1 981.8 M Gemma params without the table
+    assert abs(n(W.EX) - 311.4e6) < 0.5e6       # 311.4 M expert params
+    assert "model.action_time_mlp_in.weight" in shapes and shapes["model.action_time_mlp_in.weight"] == (1024, 2048)
+
+
+def test_packing_on_cpu_matches_definitions():
+    dims = W.Dims(n_siglip_layers=1, n_gemma_layers=1, vocab=32)
+    sd = W.random_state_dict(dims, seed=7)
+    again = W.random_state_dict(dims, seed=7)
+    assert all(torch.equal(sd[k], again[k]) for k in sd)
+    pk = W.PackedWeights(dict(sd), "cpu", torch.bfloat16)
+    assert pk.dims.n_siglip_layers == 1 and pk.dims.n_gemma_layers == 1 and pk.struct.vocab == 32
+    # GeGLU interleave: rows [0,128) of tile t are gate rows t*128.., rows [128,256) the matching up rows
+    p = f"{W.LM}layers.0.mlp."
+    wgu = next(t for t in pk.keep if t.shape == (2 * 16384, 2048))
+    assert torch.equal(wgu[256 * 3: 256 * 3 + 128], sd[p + "gate_proj.weight"][128 * 3: 128 * 4])
+    assert torch.equal(wgu[256 * 3 + 128: 256 * 4], sd[p + "up_proj.weight"][128 * 3: 128 * 4])
+    # time bias == b + W[:, 1024:] . bf16(time_emb(t_k))
+    w_in = sd["model.action_time_mlp_in.weight"].double()
+    temb = W.sinusoidal_time_embedding(W.euler_times(10)).to(torch.bfloat16).double()
+    exp = sd["model.action_time_mlp_in.bias"].double()[None] + temb @ w_in[:, 1024:].t()
+    assert torch.allclose(pk.time_bias.double(), exp, atol=1e-6)
+    assert pk.time_bias.shape == (10, 1024)
+
+
+def test_header_symbols_all_exported_and_bound():
+    """Every function include/pi0b200.h declares is exported by libpi0b200.so and typed in the binding."""
+    hdr = open(os.path.join(ROOT, "include", "pi0b200.h")).read()
+    declared = set(re.findall(r"\b(pi0_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"pi0_model_cfg", "pi0_weights", "pi0_ctx", "pi0_gemm_desc"}
+    assert declared == set(pb.SIGNATURES), declared ^ set(pb.SIGNATURES)
+    assert os.path.exists(pb.LIB_PATH), "build the library first: python int-act_b200/build.py"
+    handle = ctypes.CDLL(pb.LIB_PATH)
+    for name in declared:
+        assert hasattr(handle, name), name
+    lib = pb.lib()
+    assert lib.pi0_abi_version() == pb.ABI_VERSION
+    # host-only entry points work without a GPU
+    cfg = pb.ModelCfg(n_cams=1, lang_len=72, horizon=4, max_state_dim=32, max_action_dim=32, num_steps=10, dtype=0,
+                      max_batch=2, num_sms=148, n_siglip_layers=27, n_gemma_layers=18)
+    assert lib.pi0_workspace_bytes(ctypes.byref(cfg)) > 0
+    cfg.lang_len = 70
+    assert lib.pi0_workspace_bytes(ctypes.byref(cfg)) == 0
+    assert b"lang_len" in lib.pi0_last_error()
+    assert ctypes.sizeof(pb.Weights) == 8 * (3 + 27 * 12 + 4 + 2 + 18 * 6 * 2 + 1 + 10 + 2) + 8
+
+
+def test_policy_fails_loudly_without_cuda():
+    from int_act_b200.policy import PI0Policy, SyntheticTokenizer
+
+    tok = SyntheticTokenizer(1000)
+    ids, mask = tok(["put the carrot on the plate\n", "x\n"], 72)
+    assert ids.shape == (2, 72) and ids[0, 0] == 2 and ids[0, int(mask[0].sum()) - 1] == 108 and mask[0].sum() == 8
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    pol = PI0Policy(bridge_config(), dims=W.Dims(n_siglip_layers=1, n_gemma_layers=1, vocab=1000), tokenizer=tok)
+    batch = {"observation.images.top": torch.zeros(1, 3, 224, 224), "observation.state": torch.zeros(1, 7),
+             "task": ["pick"]}
+    with pytest.raises(pb.Pi0Error):
+        pol.select_action(batch)
