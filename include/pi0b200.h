@@ -141,6 +141,12 @@ int pi0_infer(pi0_ctx* ctx, int B, const float* const* images, float img_scale, 
 /* Introspection for the parity tests (device pointers into the workspace; element type = cfg dtype) */
 const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems);
 
+/* Per-launch CUDA-event timing for bench.py's roofline: enable, run pi0_infer once (NOT under graph capture), then
+ * pi0_profile_report writes {"label": [total_ms, launches], ...} (JSON) into buf. Reporting synchronises on the
+ * recorded events; the product path leaves profiling off. */
+int pi0_profile(pi0_ctx* ctx, int enable);
+int pi0_profile_report(pi0_ctx* ctx, char* buf, size_t buf_bytes);
+
 /* kernels launched by this library since the last call with reset != 0 (bench "gpu_launches") */
 long long pi0_launch_count(int reset);
 

@@ -90,6 +90,8 @@ SIGNATURES = {
     "pi0_infer": (C.c_int, [c_ptr, C.c_int, C.POINTER(c_ptr), C.c_float, C.c_float, c_ptr, c_ptr, c_ptr, c_ptr,
                             c_ptr, c_ptr]),
     "pi0_debug_buffer": (c_ptr, [c_ptr, C.c_char_p, C.POINTER(C.c_int64)]),
+    "pi0_profile": (C.c_int, [c_ptr, C.c_int]),
+    "pi0_profile_report": (C.c_int, [c_ptr, C.c_char_p, C.c_size_t]),
     "pi0_launch_count": (C.c_longlong, [C.c_int]),
     "pi0_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_int, C.c_int, c_ptr]),
     "pi0_rmsnorm": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),

@@ -98,55 +98,84 @@ __device__ __forceinline__ int64_t epi_out_row(const EpiParams& ep, int row) {
 }
 
 // ---- EPI_STORE: bias, alpha, post scale, activation, residual; optional transposed V region -----
+// Written as whole-chunk passes: every feature test is one uniform branch per 32-column chunk and every pass is a
+// straight-line loop over 32 independent elements, so a single epilogue warp per scheduler keeps its ALU pipe
+// busy (the element-at-a-time form was latency-bound at ~300 cycles per element).
 template <typename T>
 __device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, int col0, int N, int64_t zoff,
                                                 float* v) {
   if (col0 >= ep.vt_col0) {  // V^T region: lanes of a warp hold consecutive t => coalesced per d
-    int b = row / ep.vt_rpb, t = row % ep.vt_rpb;
+    const int b = row / ep.vt_rpb, t = row % ep.vt_rpb;
     T* vt = reinterpret_cast<T*>(ep.vt);
+    const int dall0 = col0 - ep.vt_col0;
+    int h = dall0 / ep.vt_hd, d = dall0 - h * ep.vt_hd;
+    T* dst = vt + ((int64_t)(b * ep.vt_heads + h) * ep.vt_hd + d) * ep.vt_pitch + ep.vt_toff + t;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-      int col = col0 + j;
-      if (col < N) {
-        float x = v[j] + (ep.bias ? ep.bias[col] : 0.0f);
-        int dall = col - ep.vt_col0;
-        int h = dall / ep.vt_hd, d = dall % ep.vt_hd;
-        Num<T>::st(vt + ((int64_t)(b * ep.vt_heads + h) * ep.vt_hd + d) * ep.vt_pitch + ep.vt_toff + t, x);
+      if (col0 + j < N) {
+        float x = v[j] + (ep.bias ? ep.bias[col0 + j] : 0.0f);
+        Num<T>::st(dst, x);
+        dst += ep.vt_pitch;  // (h, d) -> (h, d + 1) and (h, hd - 1) -> (h + 1, 0) are both one row further
       }
     }
     return;
   }
-  T* out = reinterpret_cast<T*>(ep.out) + zoff + epi_out_row(ep, row) * ep.ldc + col0;
-  const T* res = nullptr;
+  const int ngroups = min(4, (N - col0 + 7) >> 3);  // 8-column groups of this chunk that hold real columns
+  if (ep.bias) {
+    if (ngroups == 4) {
+      const float4* bp = reinterpret_cast<const float4*>(ep.bias + col0);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 bq = __ldg(bp + q);
+        v[4 * q] += bq.x; v[4 * q + 1] += bq.y; v[4 * q + 2] += bq.z; v[4 * q + 3] += bq.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ngroups * 8) v[j] += ep.bias[col0 + j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(v[j]);
+  if (ep.alpha != 1.0f) {
+    const float a = ep.alpha;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(v[j] * a);
+  }
+  if (ep.post_div != 0.0f) {
+    const float dv = ep.post_div;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(v[j] / dv);
+  }
+  if (ep.post_mul != 0.0f) {
+    const float m = ep.post_mul;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(v[j] * m);
+  }
+  if (ep.act == ACT_GELU_TANH) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(gelu_tanh(v[j]));
+  } else if (ep.act == ACT_SILU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(silu(v[j]));
+  }
   if (ep.res) {
-    int rrow = ep.res_row_mod > 0 ? row % ep.res_row_mod : row;
-    res = reinterpret_cast<const T*>(ep.res) + (int64_t)rrow * ep.ldr + col0;  // residuals are never batched
-  }
+    const int rrow = ep.res_row_mod > 0 ? row % ep.res_row_mod : row;
+    const T* res = reinterpret_cast<const T*>(ep.res) + (int64_t)rrow * ep.ldr + col0;  // residuals are never batched
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    int col = col0 + g * 8;
-    if (col >= N) break;
-    float t[8];
+    for (int g = 0; g < 4; ++g) {
+      if (g < ngroups) {
+        float r[8];
+        load8<T>(res + g * 8, r);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float x = v[g * 8 + j];
-      if (ep.bias) x += ep.bias[col + j];
-      x = Num<T>::rnd(x);
-      if (ep.alpha != 1.0f) x = Num<T>::rnd(x * ep.alpha);
-      if (ep.post_div != 0.0f) x = Num<T>::rnd(x / ep.post_div);
-      if (ep.post_mul != 0.0f) x = Num<T>::rnd(x * ep.post_mul);
-      if (ep.act == ACT_GELU_TANH) x = Num<T>::rnd(gelu_tanh(x));
-      else if (ep.act == ACT_SILU) x = Num<T>::rnd(silu(x));
-      t[j] = x;
+        for (int j = 0; j < 8; ++j) v[g * 8 + j] += r[j];
+      }
     }
-    if (res) {
-      float r[8];
-      load8<T>(res + g * 8, r);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) t[j] += r[j];
-    }
-    store8<T>(out + g * 8, t);
   }
+  T* out = reinterpret_cast<T*>(ep.out) + zoff + epi_out_row(ep, row) * ep.ldc + col0;
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+    if (g < ngroups) store8<T>(out + g * 8, v + g * 8);
 }
 
 // ---- EPI_GEGLU: out = gelu_tanh(gate) * up, gate/up interleaved per N tile at pack time ------------
@@ -179,12 +208,19 @@ __device__ __forceinline__ void epi_rope_chunk(const EpiParams& ep, int row, int
     if (pos < 0) pos = 0;  // leading pad tokens have cumsum(pad)-1 == -1; their K/V are never attended
     const float* cs = ep.rope_cos + (int64_t)pos * 128 + c * 32;
     const float* sn = ep.rope_sin + (int64_t)pos * 128 + c * 32;
+    const float4* c4 = reinterpret_cast<const float4*>(cs);
+    const float4* s4 = reinterpret_cast<const float4*>(sn);
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      float a = Num<T>::rnd(x1[j]), b = Num<T>::rnd(x2[j]);
-      float cj = cs[j], sj = sn[j];
-      o1[j] = a * cj - b * sj;
-      o2[j] = b * cj + a * sj;
+    for (int q = 0; q < 8; ++q) {
+      const float4 cq = __ldg(c4 + q), sq = __ldg(s4 + q);
+      const float cc[4] = {cq.x, cq.y, cq.z, cq.w}, ss[4] = {sq.x, sq.y, sq.z, sq.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int j = 4 * q + e;
+        float a = Num<T>::rnd(x1[j]), b = Num<T>::rnd(x2[j]);
+        o1[j] = a * cc[e] - b * ss[e];
+        o2[j] = b * cc[e] + a * ss[e];
+      }
     }
   } else {
 #pragma unroll

@@ -1,7 +1,7 @@
 // tcgen05 / TMEM / TMA GEMM for sm_100a:  C[z][M,N] = A[z][M,K] . W[z][N,K]^T, bf16 in, fp32 accumulate.
 //
 // Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM owner),
-// warps 2..5 = epilogue (one TMEM lane quadrant each). Operand tiles are 128 x 64 (A) and BN x 64 (W),
+// warps 2..9 = epilogue (two warps per TMEM lane quadrant, each taking half of the tile's columns). Operand tiles are 128 x 64 (A) and BN x 64 (W),
 // K-major with the 128-byte swizzle that TMA writes and the UMMA smem descriptor reads.
 // The fp32 accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps
 // the main loop of tile i+1. Tiles are visited in groups of 8 M-tiles per N sweep to keep both operand
@@ -14,7 +14,7 @@ namespace pi0 {
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGroupM = 8;
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps (2 per TMEM lane quadrant)
 
 template <int BN>
 struct TcCfg {
@@ -71,7 +71,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 4);
+      mbar_init(&tempty_bar[a], 8);
     }
     fence_barrier_init();
   }
@@ -136,7 +136,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else {
     // ------------------------------ epilogue ----------------------------------
-    const int quad = warp & 3;  // TMEM lanes [32*quad, 32*quad+32) are the ones this warp may read
+    const int quad = warp & 3;          // TMEM lanes [32*quad, 32*quad+32) are the ones this warp may read
+    const int half = (warp - 2) >> 2;   // which half of the tile's columns this warp drains
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
@@ -152,8 +153,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
       if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
         const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
+        constexpr int kChunks = BN / 32 >= 2 ? BN / 64 : 1;  // chunks per half
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = half * kChunks; c < (BN / 32 >= 2 ? (half + 1) * kChunks : 1 - half); ++c) {
           const int col0 = n0 + c * 32;
           if (col0 >= sh.N) break;
           float v[32];
@@ -168,7 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // tile columns [0, BN/2) are gate rows, [BN/2, BN) the matching up rows (interleaved at pack time)
         const int n_out = sh.N / 2;
 #pragma unroll 1
-        for (int c = 0; c < BN / 64; ++c) {
+        for (int c = half * (BN / 128); c < (half + 1) * (BN / 128); ++c) {
           const int out_col0 = tn * (BN / 2) + c * 32;
           if (out_col0 >= n_out) break;
           float g[32], u[32];
@@ -181,7 +183,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
         const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = half * 2; c < half * 2 + 2; ++c) {
           float x1[32], x2[32];
           tmem_ld_32x32(taddr + c * 32, x1);
           tmem_ld_32x32(taddr + 128 + c * 32, x2);

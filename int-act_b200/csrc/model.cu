@@ -10,7 +10,10 @@
 //   embed_suffix        modeling_mvla.py:643-694               denoise_step     modeling_mvla.py:806-839
 //   Euler loop          modeling_mvla.py:787-803
 #include <cstring>
+#include <map>
 #include <new>
+#include <string>
+#include <vector>
 
 #include "../../include/pi0b200.h"
 #include "elementwise.cuh"
@@ -56,9 +59,27 @@ struct pi0_ctx {
   int *prefix_pos, *suffix_pos, *suffix_cum;
   Buf bufs[40];
   int nbufs;
+  // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
+  bool prof_on;
+  struct ProfRec { const char* label; cudaEvent_t e0, e1; };
+  std::vector<ProfRec> prof;
 };
 
 namespace {
+
+// Records a CUDA-event pair around the launches issued while it is alive (only when profiling is enabled).
+struct ProfScope {
+  pi0_ctx* c; cudaStream_t s; cudaEvent_t e1;
+  ProfScope(pi0_ctx* ctx, const char* label, cudaStream_t st) : c(ctx), s(st), e1(nullptr) {
+    if (!c->prof_on) return;
+    cudaEvent_t e0;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { e1 = nullptr; return; }
+    cudaEventRecord(e0, s);
+    c->prof.push_back(pi0_ctx::ProfRec{label, e0, e1});
+  }
+  ~ProfScope() { if (e1) cudaEventRecord(e1, s); }
+};
+#define PROF(label) ProfScope _prof_scope(c, label, s)
 
 // ---- workspace carving (shared by pi0_workspace_bytes and pi0_ctx_create) ------------------------------
 struct Carver {
@@ -147,38 +168,45 @@ __global__ void suffix_cum_kernel(int* cum, int S) {
 inline void* at(void* p, int64_t elems, int es) { return (uint8_t*)p + elems * es; }
 inline const void* at(const void* p, int64_t elems, int es) { return (const uint8_t*)p + elems * es; }
 
-int run_gemm(pi0_ctx* c, const GemmProblem& g, cudaStream_t s) {
+int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s) {
+  PROF(label);
   return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s);
 }
 
-int run_rmsnorm(pi0_ctx* c, const void* x, void* y, const float* g, int M, int D, int rpb_in, int rpb_out, int off,
+int run_rmsnorm(pi0_ctx* c, const char* label, const void* x, void* y, const float* g, int M, int D, int rpb_in, int rpb_out, int off,
                 cudaStream_t s) {
+  PROF(label);
   if (c->cfg.dtype == 1) return rmsnorm<float>((const float*)x, (float*)y, g, M, D, kEps, rpb_in, rpb_out, off, s);
   return rmsnorm<bf16>((const bf16*)x, (bf16*)y, g, M, D, kEps, rpb_in, rpb_out, off, s);
 }
-int run_layernorm(pi0_ctx* c, const void* x, void* y, const float* w, const float* b, int M, int D, cudaStream_t s) {
+int run_layernorm(pi0_ctx* c, const char* label, const void* x, void* y, const float* w, const float* b, int M, int D,
+                  cudaStream_t s) {
+  PROF(label);
   if (c->cfg.dtype == 1) return layernorm<float>((const float*)x, (float*)y, w, b, M, D, kEps, s);
   return layernorm<bf16>((const bf16*)x, (bf16*)y, w, b, M, D, kEps, s);
 }
-int run_softmax(pi0_ctx* c, void* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
+int run_softmax(pi0_ctx* c, const char* label, void* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
                 const uint8_t* pad, int pad_pitch, const int* cum, int heads, cudaStream_t s) {
+  PROF(label);
   if (c->cfg.dtype == 1)
     return softmax_rows<float>((float*)sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads,
                                s);
   return softmax_rows<bf16>((bf16*)sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads, s);
 }
-int run_cast(pi0_ctx* c, const float* in, void* out, int64_t n, cudaStream_t s) {
+int run_cast(pi0_ctx* c, const char* label, const float* in, void* out, int64_t n, cudaStream_t s) {
+  PROF(label);
   if (c->cfg.dtype == 1) return cast_f32<float>(in, (float*)out, n, s);
   return cast_f32<bf16>(in, (bf16*)out, n, s);
 }
 
-// pick the N tile of the tcgen05 kernel so that the tile count fills the SMs reasonably
+// pick the N tile of the tcgen05 kernel: 128x256 tiles run the MMA at full rate (128-wide tiles are bound by the
+// shared-memory operand bandwidth of a single CTA), so take them whenever they still give every SM a tile
 int pick_bn(int M, int N) {
-  const int tm = (M + 127) / 128;
-  if (N % 256 == 0 && (int64_t)tm * (N / 256) >= 148) return 256;
-  if ((int64_t)tm * ((N + 127) / 128) >= 148) return 128;
-  if ((int64_t)tm * ((N + 63) / 64) >= 120) return 64;
-  return N >= 64 ? (tm * ((N + 63) / 64) >= 64 ? 64 : 32) : 32;
+  const int64_t tm = (M + 127) / 128;
+  if (N >= 256 && tm * ((N + 255) / 256) >= 120) return 256;
+  if (N >= 128 && tm * ((N + 127) / 128) >= 120) return 128;
+  if (N >= 64 && tm * ((N + 63) / 64) >= 64) return 64;
+  return 32;
 }
 
 // ---- one Gemma-style layer (prefill when suffix == false, expert over the cached prefix otherwise) ----
@@ -201,12 +229,18 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   void* att = suffix ? c->att_e : c->att_p;
   void* act = suffix ? c->act_e : c->act_p;
   const int toff = suffix ? c->P : 0;
+  static const char* kLbl[2][9] = {
+      {"prefill.rmsnorm", "prefill.qkv_rope", "prefill.scores", "prefill.softmax", "prefill.pv", "prefill.o_proj",
+       "prefill.rmsnorm", "prefill.gateup_geglu", "prefill.down"},
+      {"denoise.rmsnorm", "denoise.qkv_rope", "denoise.scores", "denoise.softmax", "denoise.pv", "denoise.o_proj",
+       "denoise.rmsnorm", "denoise.gateup_geglu", "denoise.down"}};
+  const char* const* L = kLbl[suffix ? 1 : 0];
   const int n_keys = suffix ? c->P + c->S : c->P;
   void* kc = at(c->kcache, (int64_t)layer * c->maxB * c->kv_pitch * kHd, es);
   void* vt = at(c->vtcache, (int64_t)layer * c->maxB * kHd * c->vt_pitch, es);
 
   // input RMSNorm
-  PI0_TRY(run_rmsnorm(c, io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
+  PI0_TRY(run_rmsnorm(c, L[0], io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
 
   // fused QKV + RoPE; K and V^T land in the cache (mllm.py:216-221 + fill_kv_cache)
   {
@@ -217,7 +251,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     g.epi.pos_ids = suffix ? c->suffix_pos : c->prefix_pos;
     g.epi.kcache = kc; g.epi.kv_pitch = c->kv_pitch; g.epi.n_q_heads = kHeads;
     g.epi.vt = vt; g.epi.vt_pitch = c->vt_pitch; g.epi.vt_rpb = T; g.epi.vt_toff = toff;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[1], g, s));
   }
   if (kv_only) return 0;
 
@@ -225,13 +259,13 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   {
     GemmProblem g = gemm_problem(q, kHd, kc, kHd, T * kHeads, n_keys, kHd);
     g.nz0 = B; g.a_z0 = (int64_t)T * kHeads * kHd; g.w_z0 = (int64_t)c->kv_pitch * kHd;
-    g.bn = n_keys > 256 ? 128 : 64;
+    g.bn = pick_bn(B * 128 * ((T * kHeads + 127) / 128), n_keys);
     g.epi.out = sc; g.epi.ldc = c->sc_pitch; g.epi.out_z0 = (int64_t)T * kHeads * c->sc_pitch;
     g.epi.alpha = 0.0625f;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[2], g, s));
   }
   // masked softmax (mllm.py:299-307); prefix keys gated by pad, suffix keys by the block-causal cumsum rule
-  PI0_TRY(run_softmax(c, sc, (int64_t)B * T * kHeads, T * kHeads, c->sc_pitch, n_keys, c->P, c->pad, c->P,
+  PI0_TRY(run_softmax(c, L[3], sc, (int64_t)B * T * kHeads, T * kHeads, c->sc_pitch, n_keys, c->P, c->pad, c->P,
                       suffix ? c->suffix_cum : nullptr, kHeads, s));
   // att[b, t*8+h, :] = probs . V   (V^T is the K-major operand)
   {
@@ -239,28 +273,28 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     g.nz0 = B; g.a_z0 = (int64_t)T * kHeads * c->sc_pitch; g.w_z0 = (int64_t)kHd * c->vt_pitch;
     g.bn = 256;
     g.epi.out = att; g.epi.ldc = kHd; g.epi.out_z0 = (int64_t)T * kHeads * kHd;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[4], g, s));
   }
   // o_proj + residual
   {
     GemmProblem g = gemm_problem(att, kHidden, w.wo, kHidden, M, hidden, kHidden);
     g.bn = pick_bn(M, hidden);
     g.epi.out = io.y; g.epi.ldc = hidden; g.epi.res = io.x_in; g.epi.ldr = hidden;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[5], g, s));
   }
-  PI0_TRY(run_rmsnorm(c, io.y, h, w.g2, M, hidden, 0, 0, 0, s));
+  PI0_TRY(run_rmsnorm(c, L[6], io.y, h, w.g2, M, hidden, 0, 0, 0, s));
   // GeGLU: gate/up interleaved per 256-row tile at pack time
   {
     GemmProblem g = gemm_problem(h, hidden, w.wgu, hidden, M, 2 * inter, hidden);
     g.epi_mode = EPI_GEGLU; g.bn = 256;
     g.epi.out = act; g.epi.ldc = inter;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[7], g, s));
   }
   {
     GemmProblem g = gemm_problem(act, inter, w.wdown, inter, M, hidden, inter);
     g.bn = pick_bn(M, hidden);
     g.epi.out = io.x_out; g.epi.ldc = hidden; g.epi.res = io.y; g.epi.ldr = hidden;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, L[8], g, s));
   }
   return 0;
 }
@@ -296,6 +330,7 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   c->cfg = *cfg;
   c->w = *w;
   c->nbufs = 0;
+  c->prof_on = false;
   uintptr_t b = ((uintptr_t)workspace + 1023) & ~(uintptr_t)1023;
   c->base = (uint8_t*)b;
   c->ws_bytes = workspace_bytes;
@@ -307,7 +342,47 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   return 0;
 }
 
-void pi0_ctx_destroy(pi0_ctx* ctx) { delete ctx; }
+static void prof_clear(pi0_ctx* c) {
+  for (auto& r : c->prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  c->prof.clear();
+}
+
+void pi0_ctx_destroy(pi0_ctx* ctx) {
+  if (ctx) prof_clear(ctx);
+  delete ctx;
+}
+
+int pi0_profile(pi0_ctx* c, int enable) {
+  PI0_REQUIRE(c != nullptr, "null ctx");
+  prof_clear(c);
+  c->prof_on = enable != 0;
+  return 0;
+}
+
+int pi0_profile_report(pi0_ctx* c, char* buf, size_t buf_bytes) {
+  PI0_REQUIRE(c != nullptr && buf != nullptr && buf_bytes > 2, "pi0_profile_report: bad arguments");
+  std::map<std::string, std::pair<double, int>> agg;
+  std::vector<std::string> order;
+  for (auto& r : c->prof) {
+    PI0_CHECK_CUDA(cudaEventSynchronize(r.e1));
+    float ms = 0.f;
+    PI0_CHECK_CUDA(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    auto it = agg.find(r.label);
+    if (it == agg.end()) { agg[r.label] = {ms, 1}; order.push_back(r.label); }
+    else { it->second.first += ms; it->second.second += 1; }
+  }
+  std::string out = "{";
+  for (size_t i = 0; i < order.size(); ++i) {
+    char tmp[160];
+    snprintf(tmp, sizeof(tmp), "%s\"%s\": [%.6f, %d]", i ? ", " : "", order[i].c_str(), agg[order[i]].first,
+             agg[order[i]].second);
+    out += tmp;
+  }
+  out += "}";
+  PI0_REQUIRE(out.size() + 1 <= buf_bytes, "pi0_profile_report: buffer too small (%zu needed)", out.size() + 1);
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return 0;
+}
 
 const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems) {
   if (!ctx || !name) return nullptr;
@@ -334,38 +409,41 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
 
   // patch embedding as a GEMM over the fused im2col / normalise (modeling_mvla.py:366-367 + Conv2d k14 s14),
   // bias and position embedding in the epilogue
-  if (c->cfg.dtype == 1) PI0_TRY(im2col_patch<float>(images, (float*)c->col, B, kPatchK, scale, shift, s));
-  else PI0_TRY(im2col_patch<bf16>(images, (bf16*)c->col, B, kPatchK, scale, shift, s));
+  {
+    PROF("siglip.im2col");
+    if (c->cfg.dtype == 1) PI0_TRY(im2col_patch<float>(images, (float*)c->col, B, kPatchK, scale, shift, s));
+    else PI0_TRY(im2col_patch<bf16>(images, (bf16*)c->col, B, kPatchK, scale, shift, s));
+  }
   {
     GemmProblem g = gemm_problem(c->col, kPatchK, w.patch_w, kPatchK, M, kVisHidden, kPatchK);
     g.bn = pick_bn(M, kVisHidden);
     g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = w.patch_b;
     g.epi.res = w.pos_emb; g.epi.ldr = kVisHidden; g.epi.res_row_mod = kPatches;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, "siglip.patch_embed", g, s));
   }
   const int64_t qk_ld = 2 * kVisHidden;
   for (int l = 0; l < c->cfg.n_siglip_layers; ++l) {
     const pi0_siglip_layer_w& lw = w.sig[l];
-    PI0_TRY(run_layernorm(c, c->xs, c->hs, lw.ln1_w, lw.ln1_b, M, kVisHidden, s));
+    PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, lw.ln1_w, lw.ln1_b, M, kVisHidden, s));
     {  // fused q|k|v projection; the V columns are written transposed per head for the P.V GEMM
       GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wqkv, kVisHidden, M, 3 * kVisHidden, kVisHidden);
       g.bn = pick_bn(M, 3 * kVisHidden);
       g.epi.out = c->qk_s; g.epi.ldc = qk_ld; g.epi.bias = lw.bqkv;
       g.epi.vt = c->vt_s; g.epi.vt_col0 = 2 * kVisHidden; g.epi.vt_hd = kVisHd; g.epi.vt_heads = kVisHeads;
       g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.qkv", g, s));
     }
     {  // scores[b,h] = rnd(rnd(q k^T) * 72^-0.5), bidirectional
       GemmProblem g = gemm_problem(c->qk_s, qk_ld, at(c->qk_s, kVisHidden, es), qk_ld, kPatches, kPatches, kVisHd);
       g.nz0 = kVisHeads; g.nz1 = B;
       g.a_z0 = kVisHd; g.a_z1 = (int64_t)kPatches * qk_ld; g.w_z0 = kVisHd; g.w_z1 = (int64_t)kPatches * qk_ld;
-      g.bn = 128;
+      g.bn = 256;
       g.epi.out = c->sc_s; g.epi.ldc = kPatches; g.epi.out_z0 = (int64_t)kPatches * kPatches;
       g.epi.out_z1 = (int64_t)kVisHeads * kPatches * kPatches;
       g.epi.alpha = 0.11785113019775793f;  // 72 ** -0.5
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.scores", g, s));
     }
-    PI0_TRY(run_softmax(c, c->sc_s, (int64_t)B * kVisHeads * kPatches, kVisHeads * kPatches, kPatches, kPatches,
+    PI0_TRY(run_softmax(c, "siglip.softmax", c->sc_s, (int64_t)B * kVisHeads * kPatches, kVisHeads * kPatches, kPatches, kPatches,
                         kPatches, nullptr, 0, nullptr, 1, s));
     {  // att[b, t, h*72 + d] = probs[b,h] . V[b,h]
       GemmProblem g = gemm_problem(c->sc_s, kPatches, c->vt_s, kPatches, kPatches, kVisHd, kPatches);
@@ -375,29 +453,29 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
       g.bn = 128;
       g.epi.out = c->att_s; g.epi.ldc = kVisHidden; g.epi.out_z0 = kVisHd;
       g.epi.out_z1 = (int64_t)kPatches * kVisHidden;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.pv", g, s));
     }
     {  // out_proj + residual (in place on the residual stream: each element is read then written by one thread)
       GemmProblem g = gemm_problem(c->att_s, kVisHidden, lw.wo, kVisHidden, M, kVisHidden, kVisHidden);
       g.bn = pick_bn(M, kVisHidden);
       g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bo; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.out_proj", g, s));
     }
-    PI0_TRY(run_layernorm(c, c->xs, c->hs, lw.ln2_w, lw.ln2_b, M, kVisHidden, s));
+    PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, lw.ln2_w, lw.ln2_b, M, kVisHidden, s));
     {
       GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wfc1, kVisHidden, M, kVisInter, kVisHidden);
       g.bn = pick_bn(M, kVisInter);
       g.epi.out = c->mlp_s; g.epi.ldc = kVisInter; g.epi.bias = lw.bfc1; g.epi.act = ACT_GELU_TANH;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.fc1_gelu", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->mlp_s, kVisInter, lw.wfc2, kVisInter, M, kVisHidden, kVisInter);
       g.bn = pick_bn(M, kVisHidden);
       g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bfc2; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "siglip.fc2", g, s));
     }
   }
-  PI0_TRY(run_layernorm(c, c->xs, c->hs, w.post_ln_w, w.post_ln_b, M, kVisHidden, s));
+  PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, w.post_ln_w, w.post_ln_b, M, kVisHidden, s));
   {  // projector, "/ sqrt(2048)" of HF get_image_features and "* sqrt(2048)" of embed_prefix, written into the
      // prefix rows [b*P + cam*256, +256)
     GemmProblem g = gemm_problem(c->hs, kVisHidden, w.proj_w, kVisHidden, M, kHidden, kVisHidden);
@@ -406,7 +484,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
     g.epi.post_div = 45.254833995939045f;                    // sqrt(2048) in fp32
     g.epi.post_mul = c->cfg.dtype == 1 ? 45.254833995939045f : 45.25f;  // sqrt(2048) as a 0-dim tensor of the act dtype
     g.epi.rpb_in = kPatches; g.epi.rpb_out = c->P; g.epi.row_off = cam * kPatches;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, "siglip.projector", g, s));
   }
   return 0;
 }
@@ -416,6 +494,7 @@ int pi0_embed_language(pi0_ctx* c, int B, const int64_t* tokens, void* stream) {
   PI0_REQUIRE(tokens != nullptr, "null tokens");
   cudaStream_t s = (cudaStream_t)stream;
   const float scale = 45.254833995939045f;
+  PROF("embed.language");
   if (c->cfg.dtype == 1)
     return embed_tokens<float>(tokens, (const float*)c->w.embed, (float*)c->xp, B, c->L, c->P, c->ncam * kPatches,
                                kHidden, c->w.vocab, scale, s);
@@ -427,11 +506,14 @@ int pi0_prefill(pi0_ctx* c, int B, const uint8_t* img_masks, const uint8_t* lang
   PI0_TRY(check_batch(c, B));
   PI0_REQUIRE(img_masks != nullptr && lang_masks != nullptr, "null masks");
   cudaStream_t s = (cudaStream_t)stream;
+  {
+  PROF("prefill.masks_posids");
   PI0_TRY(build_pad(img_masks, lang_masks, c->pad, B, c->ncam, c->L, s));
   PI0_TRY(position_ids(c->pad, B, c->P, c->S, c->prefix_pos, c->suffix_pos, s));
   suffix_cum_kernel<<<1, 64, 0, s>>>(c->suffix_cum, c->S);
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
+  }
   const int NL = c->cfg.n_gemma_layers;
   for (int l = 0; l < NL; ++l) {
     // the prefill output is discarded by sample_actions (modeling_mvla.py:776): the last layer only contributes K/V
@@ -452,49 +534,49 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
   const float dt = -1.0f / (float)c->cfg.num_steps;
 
   // state_proj -> suffix row 0 of every sample (input-independent across steps)
-  PI0_TRY(run_cast(c, state, c->st_act, (int64_t)B * 32, s));
+  PI0_TRY(run_cast(c, "denoise.cast", state, c->st_act, (int64_t)B * 32, s));
   {
     GemmProblem g = gemm_problem(c->st_act, 32, w.state_w, 32, B, kExpHidden, 32);
     g.bn = 32;
     g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.state_b;
     g.epi.rpb_in = 1; g.epi.rpb_out = S; g.epi.row_off = 0;
-    PI0_TRY(run_gemm(c, g, s));
+    PI0_TRY(run_gemm(c, "denoise.state_proj", g, s));
   }
   const int n_iters = c->cfg.n_euler_iters > 0 ? c->cfg.n_euler_iters : c->cfg.num_steps;
   for (int step = 0; step < n_iters; ++step) {
     // embed_suffix: action_in_proj -> (time half folded into the bias) mlp_in -> SiLU -> mlp_out -> suffix rows 1..H
-    PI0_TRY(run_cast(c, x_t, c->xt_act, (int64_t)B * H * 32, s));
+    PI0_TRY(run_cast(c, "denoise.cast", x_t, c->xt_act, (int64_t)B * H * 32, s));
     {
       GemmProblem g = gemm_problem(c->xt_act, 32, w.action_in_w, 32, B * H, kProjW, 32);
       g.bn = 32;
       g.epi.out = c->a1; g.epi.ldc = kProjW; g.epi.bias = w.action_in_b;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "denoise.action_in", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->a1, kProjW, w.time_in_wa, kProjW, B * H, kProjW, kProjW);
       g.bn = 32;
       g.epi.out = c->a2; g.epi.ldc = kProjW; g.epi.bias = w.time_bias + (int64_t)step * kProjW;
       g.epi.act = ACT_SILU;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "denoise.time_mlp_in_silu", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->a2, kProjW, w.time_out_w, kProjW, B * H, kExpHidden, kProjW);
       g.bn = 32;
       g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.time_out_b;
       g.epi.rpb_in = H; g.epi.rpb_out = S; g.epi.row_off = 1;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "denoise.time_mlp_out", g, s));
     }
     for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
       LayerIO io{l == 0 ? c->suf : c->xe, c->ye, c->xe};
       PI0_TRY(gemma_layer(c, B, l, true, io, false, s));
     }
     // final norm on the last H rows of every sample, action_out_proj and the Euler update x_t += dt * v_t
-    PI0_TRY(run_rmsnorm(c, c->xe, c->hfin, w.exp_norm_g, B * H, kExpHidden, H, S, 1, s));
+    PI0_TRY(run_rmsnorm(c, "denoise.final_norm", c->xe, c->hfin, w.exp_norm_g, B * H, kExpHidden, H, S, 1, s));
     {
       GemmProblem g = gemm_problem(c->hfin, kExpHidden, w.action_out_w, kExpHidden, B * H, 32, kExpHidden);
       g.epi_mode = EPI_EULER; g.bn = 32;
       g.epi.out = x_t; g.epi.ldc = 32; g.epi.bias = w.action_out_b; g.epi.dt = dt;
-      PI0_TRY(run_gemm(c, g, s));
+      PI0_TRY(run_gemm(c, "denoise.out_proj_euler", g, s));
     }
   }
   return 0;

@@ -148,6 +148,24 @@ class Pi0Engine:
         self._run_static(B)
         return st["x_t"].clone()
 
+    def profile_step(self, B: int) -> Dict[str, tuple]:
+        """One eager (non-graph) pass over the static buffers of batch B with a CUDA-event pair around every launch.
+        Returns {label: (total_ms, launches)}; used by bench.py for the per-kernel roofline."""
+        import json
+
+        st = self._static(B)
+        keep = st["x_t"].clone()
+        torch.cuda.synchronize(self.device)
+        pb.check(self.lib.pi0_profile(self.ctx, 1), "pi0_profile")
+        try:
+            self._infer_raw(B, st["images"], st["img_masks"], st["tokens"], st["lang_masks"], st["state"], st["x_t"])
+            buf = C.create_string_buffer(1 << 16)
+            pb.check(self.lib.pi0_profile_report(self.ctx, buf, len(buf)), "pi0_profile_report")
+        finally:
+            self.lib.pi0_profile(self.ctx, 0)
+            st["x_t"].copy_(keep)
+        return {k: (v[0], v[1]) for k, v in json.loads(buf.value.decode()).items()}
+
     def debug_buffer(self, name: str, dtype=None) -> torch.Tensor:
         """Copy of a named workspace buffer (parity tests)."""
         n = C.c_int64()
