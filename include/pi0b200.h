@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PI0_ABI_VERSION 1
+#define PI0_ABI_VERSION 2
 
 #define PI0_SIGLIP_LAYERS 27
 #define PI0_GEMMA_LAYERS 18
@@ -156,7 +156,7 @@ typedef struct pi0_gemm_desc {
   const void* W; int64_t ldw, w_z0, w_z1;
   int32_t M, N, K, nz0, nz1;
   int32_t epi_mode;  /* 0 store, 1 geglu, 2 rope(qkv), 3 euler */
-  int32_t bn;        /* 32 / 64 / 128 / 256 */
+  int32_t bn;        /* 32 / 64 / 128 / 256; 0 = pick from the shape */
   int32_t act;       /* 0 none, 1 gelu_tanh, 2 silu */
   void* out; int64_t ldc, out_z0, out_z1;
   const float* bias;
@@ -167,6 +167,7 @@ typedef struct pi0_gemm_desc {
   const float* rope_cos; const float* rope_sin; const int32_t* pos_ids;
   void* kcache; int32_t n_q_heads; int64_t kv_pitch;
   float dt;
+  int32_t splits;    /* split-K factor = thread-block cluster size, 1..8; 0 = pick from the shape */
 } pi0_gemm_desc;
 
 /* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT. */

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libpi0b200.so")
 
 SIGLIP_LAYERS = 27
 GEMMA_LAYERS = 18
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 c_f32p = C.c_void_p  # device pointers are opaque to ctypes
 c_ptr = C.c_void_p
@@ -68,7 +68,7 @@ class GemmDesc(C.Structure):
         ("vt_rpb", C.c_int32), ("vt_toff", C.c_int32), ("vt_pitch", C.c_int64),
         ("rope_cos", c_ptr), ("rope_sin", c_ptr), ("pos_ids", c_ptr),
         ("kcache", c_ptr), ("n_q_heads", C.c_int32), ("kv_pitch", C.c_int64),
-        ("dt", C.c_float),
+        ("dt", C.c_float), ("splits", C.c_int32),
     ]
 
 
@@ -146,7 +146,8 @@ def current_stream():
 
 def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bias=None, res=None, ldr=None,
          res_row_mod=0, act=ACT_NONE, alpha=1.0, post_div=0.0, post_mul=0.0, epi_mode=EPI_STORE, bn=128,
-         nz0=1, nz1=1, a_z=(0, 0), w_z=(0, 0), out_z=(0, 0), dtype=DTYPE_BF16, impl=0, num_sms=148, **extra):
+         nz0=1, nz1=1, a_z=(0, 0), w_z=(0, 0), out_z=(0, 0), dtype=DTYPE_BF16, impl=0, num_sms=148, splits=1,
+         **extra):
     """Unit-test helper around pi0_gemm: out = A . W^T with the fused epilogue (A [M,K], W [N,K] row-major)."""
     d = GemmDesc()
     d.A, d.W, d.out = ptr(A), ptr(W), ptr(out)
@@ -161,6 +162,7 @@ def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bia
     d.out_z0, d.out_z1 = out_z
     d.nz0, d.nz1 = nz0, nz1
     d.epi_mode, d.bn, d.act = epi_mode, bn, act
+    d.splits = splits
     d.bias, d.res = ptr(bias), ptr(res)
     d.ldr = ldr if ldr is not None else (res.stride(-2) if res is not None else 0)
     d.res_row_mod = res_row_mod

@@ -24,6 +24,7 @@ int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* str
   g.nz1 = d->nz1 > 0 ? d->nz1 : 1;
   g.epi_mode = d->epi_mode;
   g.bn = d->bn;
+  g.splits = d->splits;
   EpiParams& e = g.epi;
   e.out = d->out; e.ldc = d->ldc; e.out_z0 = d->out_z0; e.out_z1 = d->out_z1;
   e.bias = d->bias; e.res = d->res; e.ldr = d->ldr; e.res_row_mod = d->res_row_mod;

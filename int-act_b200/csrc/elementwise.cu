@@ -103,9 +103,59 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x,
     Num<T>::st(yr + i, v);
   }
 }
+// Register-resident variant: one warp per row, the row is read from HBM exactly once (16-byte loads), statistics by
+// warp shuffles. D <= 32 * 8 * NCH.
+template <typename T, int NCH>
+__global__ void __launch_bounds__(256) layernorm_warp_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                             const float* __restrict__ w,
+                                                             const float* __restrict__ bias, int M, int D, float eps) {
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const int lane = threadIdx.x & 31;
+  const T* xr = x + row * D;
+  float v[NCH][8];
+  float s = 0.0f;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = (c * 32 + lane) * 8;
+    if (i < D) {
+      load8<T>(xr + i, v[c]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[c][j];
+    }
+  }
+  const float mean = warp_sum(s) / D;
+  float q = 0.0f;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = (c * 32 + lane) * 8;
+    if (i < D) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { float d = v[c][j] - mean; q += d * d; }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / D + eps);
+  T* yr = y + row * D;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = (c * 32 + lane) * 8;
+    if (i < D) {
+      float wv[8], bv[8], o[8];
+      load8<float>(w + i, wv);
+      load8<float>(bias + i, bv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mean) * rstd * wv[j] + bv[j];
+      store8<T>(yr + i, o);
+    }
+  }
+}
 template <typename T>
 int layernorm(const T* x, T* y, const float* w, const float* b, int M, int D, float eps, cudaStream_t s) {
-  layernorm_kernel<T><<<M, 256, 0, s>>>(x, y, w, b, D, eps);
+  if (D % 8 == 0 && D <= 32 * 8 * 5) {
+    layernorm_warp_kernel<T, 5><<<(M + 7) / 8, 256, 0, s>>>(x, y, w, b, M, D, eps);
+  } else {
+    layernorm_kernel<T><<<M, 256, 0, s>>>(x, y, w, b, D, eps);
+  }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -141,11 +191,47 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(const T* __restrict__ x, T
     store8<T>(yr + i, v);
   }
 }
+template <typename T, int NCH>
+__global__ void __launch_bounds__(256) rmsnorm_warp_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                           const float* __restrict__ g, int M, int D, float eps,
+                                                           int rpb_in, int rpb_out, int off) {
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= M) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t in_row = rpb_in > 0 ? (int64_t)(r / rpb_in) * rpb_out + off + (r % rpb_in) : r;
+  const T* xr = x + in_row * D;
+  float v[NCH][8];
+  float q = 0.0f;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = (c * 32 + lane) * 8;
+    if (i < D) {
+      load8<T>(xr + i, v[c]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) q += v[c][j] * v[c][j];
+    }
+  }
+  const float rs = rsqrtf(warp_sum(q) / D + eps);
+  T* yr = y + (int64_t)r * D;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = (c * 32 + lane) * 8;
+    if (i < D) {
+      float gv[8], o[8];
+      load8<float>(g + i, gv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[c][j] * rs) * gv[j];
+      store8<T>(yr + i, o);
+    }
+  }
+}
 template <typename T>
 int rmsnorm(const T* x, T* y, const float* g, int M, int D, float eps, int rpb_in, int rpb_out, int off,
             cudaStream_t s) {
   PI0_REQUIRE(D % 8 == 0, "rmsnorm: D=%d must be a multiple of 8", D);
-  rmsnorm_kernel<T><<<M, 256, 0, s>>>(x, y, g, D, eps, rpb_in, rpb_out, off);
+  if (D <= 1024) rmsnorm_warp_kernel<T, 4><<<(M + 7) / 8, 256, 0, s>>>(x, y, g, M, D, eps, rpb_in, rpb_out, off);
+  else if (D <= 2048) rmsnorm_warp_kernel<T, 8><<<(M + 7) / 8, 256, 0, s>>>(x, y, g, M, D, eps, rpb_in, rpb_out, off);
+  else rmsnorm_kernel<T><<<M, 256, 0, s>>>(x, y, g, D, eps, rpb_in, rpb_out, off);
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -200,12 +286,90 @@ __global__ void __launch_bounds__(256) softmax_kernel(T* __restrict__ sc, int64_
     Num<T>::st(p + j, expf(v - mx) * inv);
   }
 }
+// Register-resident variant: one warp per row, each lane owns NCH chunks of 8 consecutive keys, so the row crosses
+// HBM once in each direction with 16-byte accesses. Needs n_keys <= 256 * NCH, n_prefix % 8 == 0, pitch % 8 == 0.
+template <typename T, int NCH>
+__global__ void __launch_bounds__(256) softmax_warp_kernel(T* __restrict__ sc, int64_t rows_total, int rows_per_b,
+                                                           int64_t pitch, int n_keys, int n_prefix,
+                                                           const uint8_t* __restrict__ pad, int pad_pitch,
+                                                           const int* __restrict__ cum, int heads) {
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows_total) return;
+  const int lane = threadIdx.x & 31;
+  const int b = (int)(row / rows_per_b);
+  const int rq = (int)(row % rows_per_b);
+  T* p = sc + row * pitch;
+  const float kNeg = -2.3819763e38f;
+  int cq = 0;
+  if (cum != nullptr) cq = cum[rq / heads];
+  float v[NCH][8];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int j0 = (c * 32 + lane) * 8;
+    if (j0 < n_keys) {
+      load8<T>(p + j0, v[c]);
+      if (j0 < n_prefix) {
+        if (pad != nullptr) {
+          const uint2 pm = *reinterpret_cast<const uint2*>(pad + (int64_t)b * pad_pitch + j0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t wd = j < 4 ? pm.x : pm.y;
+            if (((wd >> (8 * (j & 3))) & 0xffu) == 0) v[c][j] = kNeg;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (j0 + j >= n_keys) v[c][j] = -INFINITY;          // beyond the row: not part of the softmax
+          else if (!(cum[j0 + j - n_prefix] <= cq)) v[c][j] = kNeg;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) mx = fmaxf(mx, v[c][j]);
+    }
+  }
+  mx = warp_max(mx);
+  float sum = 0.0f;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int j0 = (c * 32 + lane) * 8;
+    if (j0 < n_keys) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { v[c][j] = expf(v[c][j] - mx); sum += v[c][j]; }
+    }
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.0f / sum;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int j0 = (c * 32 + lane) * 8;
+    if (j0 < n_keys) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[c][j] *= inv;
+      store8<T>(p + j0, v[c]);
+    }
+  }
+}
 template <typename T>
 int softmax_rows(T* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
                  const uint8_t* pad, int pad_pitch, const int* cum, int heads, cudaStream_t s) {
   int64_t blocks = (rows_total + 7) / 8;
-  softmax_kernel<T><<<(unsigned)blocks, 256, 0, s>>>(sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad,
-                                                     pad_pitch, cum, heads);
+  // keys in [n_prefix, n_keys) need the cumsum rule; a prefix-only row with n_keys % 8 != 0 takes the generic kernel
+  const bool vec_ok = pitch % 8 == 0 && n_prefix % 8 == 0 && pitch >= (int64_t)((n_keys + 7) / 8) * 8 &&
+                      (pad == nullptr || pad_pitch % 8 == 0) && (n_keys == n_prefix ? n_keys % 8 == 0 : cum != nullptr) &&
+                      (reinterpret_cast<uintptr_t>(sc) % 32 == 0) &&
+                      (pad == nullptr || reinterpret_cast<uintptr_t>(pad) % 8 == 0);
+#define PI0_SM(NCH) softmax_warp_kernel<T, NCH><<<(unsigned)blocks, 256, 0, s>>>(sc, rows_total, rows_per_b, pitch, \
+                                                 n_keys, n_prefix, pad, pad_pitch, cum, heads)
+  if (vec_ok && n_keys <= 256) PI0_SM(1);
+  else if (vec_ok && n_keys <= 512) PI0_SM(2);
+  else if (vec_ok && n_keys <= 768) PI0_SM(3);
+  else if (vec_ok && n_keys <= 1024) PI0_SM(4);
+  else
+    softmax_kernel<T><<<(unsigned)blocks, 256, 0, s>>>(sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad,
+                                                       pad_pitch, cum, heads);
+#undef PI0_SM
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;

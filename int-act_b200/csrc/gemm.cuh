@@ -14,7 +14,8 @@ struct GemmProblem {
   int M, N, K;
   int nz0, nz1;             // batch grid (1,1 for a plain GEMM)
   int epi_mode;             // EpiMode
-  int bn;                   // N tile of the tcgen05 kernel (32/64/128/256); EPI_ROPE requires 256
+  int bn;                   // N tile of the tcgen05 kernel (32/64/128/256; 0 = auto); EPI_ROPE requires 256
+  int splits;               // split-K factor = cluster size (1..8; 0 = auto)
   EpiParams epi;
 };
 
@@ -23,7 +24,7 @@ inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64
   g.A = A; g.lda = lda; g.a_z0 = 0; g.a_z1 = 0;
   g.W = W; g.ldw = ldw; g.w_z0 = 0; g.w_z1 = 0;
   g.M = M; g.N = N; g.K = K; g.nz0 = 1; g.nz1 = 1;
-  g.epi_mode = EPI_STORE; g.bn = 256;
+  g.epi_mode = EPI_STORE; g.bn = 256; g.splits = 0;
   g.epi = epi_default();
   return g;
 }

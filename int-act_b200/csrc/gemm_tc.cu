@@ -31,6 +31,8 @@ struct TcShape {
   int nz0, nz1;
   int tiles_m, tiles_n;
   int total_tiles;
+  int splits;        // split-K: CTAs (= cluster size) per output tile, 1 = none
+  int kb_per_split;  // k-blocks (of kBK) per split
 };
 
 __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, int& tm, int& tn) {
@@ -205,6 +207,193 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Split-K variant for skinny problems (fewer output tiles than SMs): one thread-block CLUSTER per output tile, CTA
+// `rank` of the cluster accumulates k-blocks [rank*kb_per_split, ...) of the tile in its own TMEM, spills the fp32
+// partial into its shared memory ([col][row], reusing the drained operand ring), and after a cluster barrier every
+// CTA finalises a share of the tile's column chunks by summing the partials of all ranks IN RANK ORDER over
+// distributed shared memory (deterministic), then runs the ordinary epilogue. No global workspace, no atomics.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  __syncwarp();
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t dsmem_map(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ float dsmem_ld_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+// v[j] = sum over ranks (ascending) of partial[rank][chunk*32 + j][r]
+__device__ __forceinline__ void splitk_fetch(uint32_t stage_u32, int splits, int chunk, int r, float* v) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+  for (int s = 0; s < splits; ++s) {
+    const uint32_t base = dsmem_map(stage_u32, (uint32_t)s) + (uint32_t)(((chunk * 32) * kBM + r) * 4);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] += dsmem_ld_f32(base + (uint32_t)(j * kBM * 4));
+  }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+                      const EpiParams ep) {
+  using Cfg = TcCfg<BN>;
+  static_assert((uint32_t)BN * kBM * 4 <= Cfg::kStages * Cfg::kStageBytes, "partial tile must fit the operand ring");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int splits = sh.splits;
+  const int rank = (int)cluster_ctarank();
+  const int tile = blockIdx.x / splits;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tfull_bar[0], 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<(BN < 32 ? 32 : BN)>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_k = (sh.K + kBK - 1) / kBK;
+  const int kb0 = rank * sh.kb_per_split;
+  const int kb1 = min(num_k, kb0 + sh.kb_per_split);
+  int z, tm, tn;
+  tile_coords(sh, tile, z, tm, tn);
+  const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
+        tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint64_t da = umma_desc_k_sw128(sa);
+        const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
+#pragma unroll
+        for (int k = 0; k < kBK / 16; ++k)
+          umma_bf16(tmem_base, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+        umma_commit(&empty_bar[stage]);
+        if (kb == kb1 - 1) umma_commit(&tfull_bar[0]);
+      }
+      __syncwarp();
+      if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // spill this CTA's partial accumulator: TMEM -> smem [col][row] (the operand ring is drained once tfull fires)
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int r = quad * 32 + lane;
+    mbar_wait(&tfull_bar[0], 0);
+    tc_fence_after();
+    float* stage_f = reinterpret_cast<float*>(smem);
+    const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    constexpr int kChunks = BN / 32;
+#pragma unroll 1
+    for (int c = half; c < kChunks; c += 2) {
+      if (tn * BN + c * 32 >= sh.N) break;
+      float v[32];
+      tmem_ld_32x32(taddr + c * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) stage_f[(c * 32 + j) * kBM + r] = v[j];
+    }
+    tc_fence_before();
+  }
+  cluster_sync_all();  // every rank's partial is visible cluster-wide
+
+  if (warp >= 2) {
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int r = quad * 32 + lane;
+    const int row = tm * kBM + r;
+    const int n0 = tn * BN;
+    const uint32_t stage_u32 = smem_u32(smem);
+    if (row < sh.M) {
+      if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
+        const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
+        int i = 0;
+        for (int c = rank; c < BN / 32; c += splits, ++i) {
+          if ((i & 1) != half) continue;
+          const int col0 = n0 + c * 32;
+          if (col0 >= sh.N) break;
+          float v[32];
+          splitk_fetch(stage_u32, splits, c, r, v);
+          if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
+          else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
+        }
+      } else if constexpr (EPI == EPI_GEGLU) {
+        const int n_out = sh.N / 2;
+        int i = 0;
+        for (int c = rank; c < BN / 64; c += splits, ++i) {
+          if ((i & 1) != half) continue;
+          const int out_col0 = tn * (BN / 2) + c * 32;
+          if (out_col0 >= n_out) break;
+          float g[32], u[32];
+          splitk_fetch(stage_u32, splits, c, r, g);
+          splitk_fetch(stage_u32, splits, BN / 64 + c, r, u);
+          epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
+        }
+      } else if constexpr (EPI == EPI_ROPE) {
+        static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
+        const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
+        int i = 0;
+        for (int c = rank; c < 4; c += splits, ++i) {
+          if ((i & 1) != half) continue;
+          float x1[32], x2[32];
+          splitk_fetch(stage_u32, splits, c, r, x1);
+          splitk_fetch(stage_u32, splits, 4 + c, r, x2);
+          epi_rope_chunk<bf16>(ep, row, which, tn, c, x1, x2);
+        }
+      }
+    }
+  }
+  cluster_sync_all();  // nobody leaves while a peer may still read its partial
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc<(BN < 32 ? 32 : BN)>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -248,11 +437,13 @@ static int make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0
 }
 
 template <int BN, int EPI>
-static int launch_cfg(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_t stream) {
   using Cfg = TcCfg<BN>;
   static bool attr_set = false;
   if (!attr_set) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)Cfg::kSmemBytes));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_splitk_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytes));
     attr_set = true;
   }
@@ -264,11 +455,64 @@ static int launch_cfg(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   sh.tiles_m = (g.M + kBM - 1) / kBM;
   sh.tiles_n = (g.N + BN - 1) / BN;
   sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
-  int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
-  gemm_tc_kernel<BN, EPI><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, sh, g.epi);
+  const int num_k = (g.K + kBK - 1) / kBK;
+  sh.splits = 1;
+  sh.kb_per_split = num_k;
+  if (splits > 1) {
+    // every rank of the cluster must own at least one k-block
+    int per = (num_k + splits - 1) / splits;
+    int eff = (num_k + per - 1) / per;
+    sh.splits = eff;
+    sh.kb_per_split = per;
+  }
+  if (sh.splits > 1) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(sh.total_tiles * sh.splits), 1, 1);
+    lc.blockDim = dim3(kTcThreads, 1, 1);
+    lc.dynamicSmemBytes = Cfg::kSmemBytes;
+    lc.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)sh.splits;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, gemm_tc_splitk_kernel<BN, EPI>, tmA, tmB, sh, g.epi));
+  } else {
+    int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
+    gemm_tc_kernel<BN, EPI><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, sh, g.epi);
+  }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
+}
+
+// Tile / split choice for the plain-store epilogue (bn == 0 => auto): maximise the number of busy SMs, prefer the
+// widest tile (fewest A re-reads) and the fewest splits among equals. Split factors are cluster sizes (<= 8).
+void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* bn_io, int* splits_out) {
+  const int tm = (M + kBM - 1) / kBM;
+  const int num_k = (K + kBK - 1) / kBK;
+  int best_bn = fixed_bn ? *bn_io : 256, best_s = 1;
+  long best_score = -1;
+  const int cands[4] = {256, 128, 64, 32};
+  for (int ci = 0; ci < 4; ++ci) {
+    const int bn = cands[ci];
+    if (fixed_bn && bn != *bn_io) continue;
+    if (!fixed_bn && bn == 32) continue;
+    if (!fixed_bn && bn > 64 && N < bn) continue;
+    const long tiles = (long)tm * ((N + bn - 1) / bn) * nz;
+    for (int sp = 1; sp <= 8; ++sp) {
+      if (sp > 1 && (tiles * sp > num_sms || num_k / sp < 2)) break;
+      long busy = tiles * sp < num_sms ? tiles * sp : num_sms;
+      // full waves only matter once there are more tiles than SMs; a partial second wave costs a whole one
+      if (tiles > num_sms) busy = num_sms * tiles / (((tiles + num_sms - 1) / num_sms) * num_sms);
+      long score = busy * 1000 + (bn >> 5) * 8 - sp;
+      if (score > best_score) { best_score = score; best_bn = bn; best_s = sp; }
+    }
+  }
+  *bn_io = best_bn;
+  *splits_out = best_s;
 }
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
@@ -278,28 +522,36 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
                          g.epi.ldc >= (int64_t)((g.N + 7) / 8) * 8;
   PI0_REQUIRE(g.N % 8 == 0 || g.epi_mode == EPI_EULER || g.epi.vt != nullptr || ragged_ok,
               "gemm_tc: N=%d must be a multiple of 8", g.N);
+  int bn = g.bn, sp = g.splits;
+  if (sp == 0 || bn == 0) {
+    int auto_s = 1;
+    const bool fixed = bn != 0;
+    gemm_tc_pick(g.M, g.N, g.K, g.nz0 * g.nz1, num_sms, fixed, &bn, &auto_s);
+    if (sp == 0) sp = auto_s;
+  }
+  PI0_REQUIRE(sp >= 1 && sp <= 8, "gemm_tc: splits=%d outside [1,8]", sp);
   switch (g.epi_mode) {
     case EPI_STORE:
-      switch (g.bn) {
-        case 256: return launch_cfg<256, EPI_STORE>(g, num_sms, stream);
-        case 128: return launch_cfg<128, EPI_STORE>(g, num_sms, stream);
-        case 64: return launch_cfg<64, EPI_STORE>(g, num_sms, stream);
-        case 32: return launch_cfg<32, EPI_STORE>(g, num_sms, stream);
+      switch (bn) {
+        case 256: return launch_cfg<256, EPI_STORE>(g, num_sms, sp, stream);
+        case 128: return launch_cfg<128, EPI_STORE>(g, num_sms, sp, stream);
+        case 64: return launch_cfg<64, EPI_STORE>(g, num_sms, sp, stream);
+        case 32: return launch_cfg<32, EPI_STORE>(g, num_sms, sp, stream);
       }
       break;
     case EPI_GEGLU:
       PI0_REQUIRE(g.N % 256 == 0, "gemm_tc: GeGLU N=%d must be a multiple of 256", g.N);
-      if (g.bn == 256) return launch_cfg<256, EPI_GEGLU>(g, num_sms, stream);
+      if (bn == 256) return launch_cfg<256, EPI_GEGLU>(g, num_sms, sp, stream);
       break;
     case EPI_ROPE:
       PI0_REQUIRE(g.N == (g.epi.n_q_heads + 2) * 256, "gemm_tc: RoPE epilogue expects N = (q_heads + 2) * 256");
-      if (g.bn == 256) return launch_cfg<256, EPI_ROPE>(g, num_sms, stream);
+      if (bn == 256) return launch_cfg<256, EPI_ROPE>(g, num_sms, sp, stream);
       break;
     case EPI_EULER:
-      if (g.bn == 32) return launch_cfg<32, EPI_EULER>(g, num_sms, stream);
+      if (bn == 32) return launch_cfg<32, EPI_EULER>(g, num_sms, sp, stream);
       break;
   }
-  set_error("gemm_tc: unsupported epilogue/tile combination epi=%d bn=%d", g.epi_mode, g.bn);
+  set_error("gemm_tc: unsupported epilogue/tile combination epi=%d bn=%d", g.epi_mode, bn);
   return -2;
 }
 

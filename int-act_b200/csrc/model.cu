@@ -199,16 +199,6 @@ int run_cast(pi0_ctx* c, const char* label, const float* in, void* out, int64_t 
   return cast_f32<bf16>(in, (bf16*)out, n, s);
 }
 
-// pick the N tile of the tcgen05 kernel: 128x256 tiles run the MMA at full rate (128-wide tiles are bound by the
-// shared-memory operand bandwidth of a single CTA), so take them whenever they still give every SM a tile
-int pick_bn(int M, int N) {
-  const int64_t tm = (M + 127) / 128;
-  if (N >= 256 && tm * ((N + 255) / 256) >= 120) return 256;
-  if (N >= 128 && tm * ((N + 127) / 128) >= 120) return 128;
-  if (N >= 64 && tm * ((N + 63) / 64) >= 64) return 64;
-  return 32;
-}
-
 // ---- one Gemma-style layer (prefill when suffix == false, expert over the cached prefix otherwise) ----
 struct LayerIO {
   const void* x_in;  // residual stream in  [M, hidden]
@@ -259,7 +249,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   {
     GemmProblem g = gemm_problem(q, kHd, kc, kHd, T * kHeads, n_keys, kHd);
     g.nz0 = B; g.a_z0 = (int64_t)T * kHeads * kHd; g.w_z0 = (int64_t)c->kv_pitch * kHd;
-    g.bn = pick_bn(B * 128 * ((T * kHeads + 127) / 128), n_keys);
+    g.bn = 0;
     g.epi.out = sc; g.epi.ldc = c->sc_pitch; g.epi.out_z0 = (int64_t)T * kHeads * c->sc_pitch;
     g.epi.alpha = 0.0625f;
     PI0_TRY(run_gemm(c, L[2], g, s));
@@ -278,7 +268,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   // o_proj + residual
   {
     GemmProblem g = gemm_problem(att, kHidden, w.wo, kHidden, M, hidden, kHidden);
-    g.bn = pick_bn(M, hidden);
+    g.bn = 0;
     g.epi.out = io.y; g.epi.ldc = hidden; g.epi.res = io.x_in; g.epi.ldr = hidden;
     PI0_TRY(run_gemm(c, L[5], g, s));
   }
@@ -292,7 +282,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   }
   {
     GemmProblem g = gemm_problem(act, inter, w.wdown, inter, M, hidden, inter);
-    g.bn = pick_bn(M, hidden);
+    g.bn = 0;
     g.epi.out = io.x_out; g.epi.ldc = hidden; g.epi.res = io.y; g.epi.ldr = hidden;
     PI0_TRY(run_gemm(c, L[8], g, s));
   }
@@ -416,7 +406,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
   }
   {
     GemmProblem g = gemm_problem(c->col, kPatchK, w.patch_w, kPatchK, M, kVisHidden, kPatchK);
-    g.bn = pick_bn(M, kVisHidden);
+    g.bn = 0;
     g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = w.patch_b;
     g.epi.res = w.pos_emb; g.epi.ldr = kVisHidden; g.epi.res_row_mod = kPatches;
     PI0_TRY(run_gemm(c, "siglip.patch_embed", g, s));
@@ -427,7 +417,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
     PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, lw.ln1_w, lw.ln1_b, M, kVisHidden, s));
     {  // fused q|k|v projection; the V columns are written transposed per head for the P.V GEMM
       GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wqkv, kVisHidden, M, 3 * kVisHidden, kVisHidden);
-      g.bn = pick_bn(M, 3 * kVisHidden);
+      g.bn = 0;
       g.epi.out = c->qk_s; g.epi.ldc = qk_ld; g.epi.bias = lw.bqkv;
       g.epi.vt = c->vt_s; g.epi.vt_col0 = 2 * kVisHidden; g.epi.vt_hd = kVisHd; g.epi.vt_heads = kVisHeads;
       g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
@@ -457,20 +447,20 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
     }
     {  // out_proj + residual (in place on the residual stream: each element is read then written by one thread)
       GemmProblem g = gemm_problem(c->att_s, kVisHidden, lw.wo, kVisHidden, M, kVisHidden, kVisHidden);
-      g.bn = pick_bn(M, kVisHidden);
+      g.bn = 0;
       g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bo; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
       PI0_TRY(run_gemm(c, "siglip.out_proj", g, s));
     }
     PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, lw.ln2_w, lw.ln2_b, M, kVisHidden, s));
     {
       GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wfc1, kVisHidden, M, kVisInter, kVisHidden);
-      g.bn = pick_bn(M, kVisInter);
+      g.bn = 0;
       g.epi.out = c->mlp_s; g.epi.ldc = kVisInter; g.epi.bias = lw.bfc1; g.epi.act = ACT_GELU_TANH;
       PI0_TRY(run_gemm(c, "siglip.fc1_gelu", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->mlp_s, kVisInter, lw.wfc2, kVisInter, M, kVisHidden, kVisInter);
-      g.bn = pick_bn(M, kVisHidden);
+      g.bn = 0;
       g.epi.out = c->xs; g.epi.ldc = kVisHidden; g.epi.bias = lw.bfc2; g.epi.res = c->xs; g.epi.ldr = kVisHidden;
       PI0_TRY(run_gemm(c, "siglip.fc2", g, s));
     }
@@ -479,7 +469,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
   {  // projector, "/ sqrt(2048)" of HF get_image_features and "* sqrt(2048)" of embed_prefix, written into the
      // prefix rows [b*P + cam*256, +256)
     GemmProblem g = gemm_problem(c->hs, kVisHidden, w.proj_w, kVisHidden, M, kHidden, kVisHidden);
-    g.bn = pick_bn(M, kHidden);
+    g.bn = 0;
     g.epi.out = c->xp; g.epi.ldc = kHidden; g.epi.bias = w.proj_b;
     g.epi.post_div = 45.254833995939045f;                    // sqrt(2048) in fp32
     g.epi.post_mul = c->cfg.dtype == 1 ? 45.254833995939045f : 45.25f;  // sqrt(2048) as a 0-dim tensor of the act dtype
@@ -537,7 +527,7 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
   PI0_TRY(run_cast(c, "denoise.cast", state, c->st_act, (int64_t)B * 32, s));
   {
     GemmProblem g = gemm_problem(c->st_act, 32, w.state_w, 32, B, kExpHidden, 32);
-    g.bn = 32;
+    g.bn = 0;
     g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.state_b;
     g.epi.rpb_in = 1; g.epi.rpb_out = S; g.epi.row_off = 0;
     PI0_TRY(run_gemm(c, "denoise.state_proj", g, s));
@@ -548,20 +538,20 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
     PI0_TRY(run_cast(c, "denoise.cast", x_t, c->xt_act, (int64_t)B * H * 32, s));
     {
       GemmProblem g = gemm_problem(c->xt_act, 32, w.action_in_w, 32, B * H, kProjW, 32);
-      g.bn = 32;
+      g.bn = 0;
       g.epi.out = c->a1; g.epi.ldc = kProjW; g.epi.bias = w.action_in_b;
       PI0_TRY(run_gemm(c, "denoise.action_in", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->a1, kProjW, w.time_in_wa, kProjW, B * H, kProjW, kProjW);
-      g.bn = 32;
+      g.bn = 0;
       g.epi.out = c->a2; g.epi.ldc = kProjW; g.epi.bias = w.time_bias + (int64_t)step * kProjW;
       g.epi.act = ACT_SILU;
       PI0_TRY(run_gemm(c, "denoise.time_mlp_in_silu", g, s));
     }
     {
       GemmProblem g = gemm_problem(c->a2, kProjW, w.time_out_w, kProjW, B * H, kExpHidden, kProjW);
-      g.bn = 32;
+      g.bn = 0;
       g.epi.out = c->suf; g.epi.ldc = kExpHidden; g.epi.bias = w.time_out_b;
       g.epi.rpb_in = H; g.epi.rpb_out = S; g.epi.row_off = 1;
       PI0_TRY(run_gemm(c, "denoise.time_mlp_out", g, s));

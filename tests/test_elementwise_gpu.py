@@ -1,0 +1,121 @@
+"""GPU unit tests of the HBM-bound kernels through the C ABI (pi0_rmsnorm / pi0_layernorm / pi0_softmax /
+pi0_position_ids) against plain PyTorch fp32 references of the same op."""
+import ctypes as C
+
+import pytest
+import torch
+
+from int_act_b200 import binding as pb
+
+pytestmark = pytest.mark.gpu
+NEG = -2.3819763e38
+
+
+def _stream():
+    return pb.current_stream()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("M,D", [(5, 1024), (333, 2048), (17, 4096), (9, 72)])
+def test_rmsnorm(cuda, dtype, M, D):
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((M, D), generator=g).to(dtype).to(cuda)
+    gain = (1.0 + 0.1 * torch.randn(D, generator=g)).to(cuda)
+    y = torch.empty_like(x)
+    pb.check(pb.lib().pi0_rmsnorm(pb.ptr(x), pb.ptr(y), pb.ptr(gain), M, D, int(dtype == torch.float32), _stream()))
+    torch.cuda.synchronize()
+    xf = x.float()
+    ref = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6) * gain).to(dtype).float()
+    tol = 1e-5 if dtype == torch.float32 else 2 ** -7
+    assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("M,D", [(256, 1152), (13, 1152), (7, 2048)])
+def test_layernorm(cuda, dtype, M, D):
+    g = torch.Generator().manual_seed(2)
+    x = (torch.randn((M, D), generator=g) * 2 + 0.3).to(dtype).to(cuda)
+    w = (1.0 + 0.1 * torch.randn(D, generator=g)).to(cuda)
+    b = (0.1 * torch.randn(D, generator=g)).to(cuda)
+    y = torch.empty_like(x)
+    pb.check(pb.lib().pi0_layernorm(pb.ptr(x), pb.ptr(y), pb.ptr(w), pb.ptr(b), M, D, int(dtype == torch.float32),
+                                    _stream()))
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.layer_norm(x.float(), (D,), w, b, 1e-6).to(dtype).float()
+    tol = 2e-5 if dtype == torch.float32 else 2 ** -7
+    assert (y.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+def _softmax_ref(sc, pad, cum, n_prefix, heads, dtype):
+    """sc [B, R, n_keys] fp32 (already rounded to dtype); pad [B, n_prefix] bool or None; cum [S] or None."""
+    B, R, n_keys = sc.shape
+    mask = torch.ones((B, R, n_keys), dtype=torch.bool)
+    if pad is not None:
+        mask[:, :, :n_prefix] = pad[:, None, :]
+    if cum is not None:
+        q = cum[torch.arange(R) // heads]                      # [R]
+        mask[:, :, n_prefix:] = (cum[None, :] <= q[:, None])[None]
+    x = torch.where(mask, sc, torch.tensor(NEG))
+    return torch.softmax(x, dim=-1).to(dtype).float()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("B,T,P,S", [(3, 328, 328, 0), (2, 5, 328, 5), (2, 17, 584, 17), (2, 256, 256, 0),
+                                     (1, 5, 1096, 5)])
+def test_masked_softmax(cuda, dtype, B, T, P, S):
+    """Prefix rows (pad gate only), suffix rows (pad gate + block-causal cumsum rule), SigLIP rows (no mask), and a
+    row longer than the register-resident kernel covers (generic fallback)."""
+    heads = 8
+    g = torch.Generator().manual_seed(3)
+    n_keys = P + S
+    pitch = (n_keys + 7) // 8 * 8
+    R = T * heads
+    sc = torch.zeros((B, R, pitch), dtype=dtype)
+    sc[:, :, :n_keys] = (torch.randn((B, R, n_keys), generator=g) * 3).to(dtype)
+    no_mask = P == 256
+    pad = None
+    if not no_mask:
+        pad = torch.ones((B, P), dtype=torch.bool)
+        pad[0, P - 60:] = False        # right-padded text
+        if B > 1:
+            pad[1, P - 1:] = False
+    cum = torch.tensor([1] + [2] * (S - 1), dtype=torch.int32) if S > 0 else None
+    d_sc = sc.to(cuda)
+    d_pad = pad.to(torch.uint8).to(cuda) if pad is not None else None
+    d_cum = cum.to(cuda) if cum is not None else None
+    pb.check(pb.lib().pi0_softmax(pb.ptr(d_sc), B * R, R, pitch, n_keys, P, pb.ptr(d_pad), P, pb.ptr(d_cum),
+                                  heads if S > 0 else 1, int(dtype == torch.float32), _stream()))
+    torch.cuda.synchronize()
+    ref = _softmax_ref(sc[:, :, :n_keys].float(), pad, cum, P, heads, dtype)
+    got = d_sc.cpu().float()[:, :, :n_keys]
+    tol = 1e-6 if dtype == torch.float32 else 2 ** -8
+    assert (got - ref).abs().max().item() <= tol
+    # masked keys carry exactly zero probability, rows sum to one
+    if pad is not None:
+        assert got[0, :, P - 60: P].abs().max().item() == 0.0
+    assert (got.sum(-1) - 1).abs().max().item() <= (1e-5 if dtype == torch.float32 else 2e-2)
+
+
+def test_fully_masked_row_is_uniform(cuda):
+    """The reference masks with a finite value, so a row whose keys are all masked is uniform, not NaN
+    ([mirror] mllm.py:301-307)."""
+    P = 64
+    sc = torch.randn((1, 8, P)).bfloat16().to(cuda)
+    pad = torch.zeros((1, P), dtype=torch.uint8, device=cuda)
+    pb.check(pb.lib().pi0_softmax(pb.ptr(sc), 8, 8, P, P, P, pb.ptr(pad), P, None, 1, 0, _stream()))
+    torch.cuda.synchronize()
+    assert torch.allclose(sc.float().cpu(), torch.full((1, 8, P), 1.0 / P).bfloat16().float())
+
+
+def test_position_ids_bit_exact(cuda):
+    B, P, S = 4, 328, 5
+    g = torch.Generator().manual_seed(4)
+    pad = torch.rand((B, P), generator=g) > 0.2
+    pad[3, :10] = False  # leading pads give -1
+    d_pad = pad.to(torch.uint8).to(cuda)
+    pp = torch.empty((B, P), dtype=torch.int32, device=cuda)
+    sp = torch.empty((B, S), dtype=torch.int32, device=cuda)
+    pb.check(pb.lib().pi0_position_ids(pb.ptr(d_pad), B, P, S, pb.ptr(pp), pb.ptr(sp), _stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(pp.cpu().long(), torch.cumsum(pad.long(), 1) - 1)
+    assert torch.equal(sp.cpu().long(), pad.sum(1)[:, None] + torch.arange(S)[None])

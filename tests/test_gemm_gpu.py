@@ -107,6 +107,63 @@ def test_gemm_geglu(cuda, impl):
     assert (out.float() - ref).abs().max().item() <= 3e-2 * max(1.0, ref.abs().max().item())
 
 
+# ---- split-K (thread-block cluster + DSMEM reduction) --------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K,bn,splits", [(5, 1024, 4096, 64, 8), (320, 1024, 2048, 256, 8), (40, 2048, 1024, 128, 3),
+                                             (328, 2048, 16384, 256, 6), (20, 1024, 1024, 32, 4), (130, 520, 1152, 256, 2),
+                                             (5, 1024, 4096, 0, 0), (320, 1024, 4096, 0, 0), (256, 1152, 4304, 0, 0)])
+def test_gemm_splitk_matches_unsplit(cuda, M, N, K, bn, splits):
+    """The cluster split-K kernel against the fp32 reference AND against the unsplit tcgen05 kernel (same bf16 result up
+    to the fp32 summation order), with bias + activation + residual in the epilogue. bn=0/splits=0 = auto pick."""
+    A = _rand((M, K), cuda, seed=21)
+    W = _rand((N, K), cuda, 0.03, seed=22)
+    bias = _rand((N,), cuda, 0.5, torch.float32, seed=23)
+    res = _rand((M, N), cuda, seed=24)
+    o_split = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    o_plain = torch.zeros_like(o_split)
+    pb.gemm(A, W, o_split, bias=bias, res=res, act=pb.ACT_SILU, bn=bn, splits=splits)
+    pb.gemm(A, W, o_plain, bias=bias, res=res, act=pb.ACT_SILU, bn=bn if bn else 128, splits=1)
+    torch.cuda.synchronize()
+    lin = (_ref_linear(A, W) + bias).bfloat16().float()
+    ref = (torch.nn.functional.silu(lin).bfloat16().float() + res.float()).bfloat16().float()
+    scale = max(1.0, ref.abs().max().item())
+    assert (o_split.float() - ref).abs().max().item() <= 3e-2 * scale
+    assert (o_split.float() - o_plain.float()).abs().max().item() <= 2 ** -6 * scale
+    # deterministic: rank-ordered DSMEM reduction
+    o_again = torch.zeros_like(o_split)
+    pb.gemm(A, W, o_again, bias=bias, res=res, act=pb.ACT_SILU, bn=bn, splits=splits)
+    torch.cuda.synchronize()
+    assert torch.equal(o_again, o_split)
+
+
+@pytest.mark.parametrize("splits", [2, 4])
+def test_gemm_geglu_splitk(cuda, splits):
+    M, K, inter = 37, 1024, 1024
+    A = _rand((M, K), cuda, seed=31)
+    Wg = _rand((inter, K), cuda, 0.03, seed=32)
+    Wu = _rand((inter, K), cuda, 0.03, seed=33)
+    Wgu = torch.stack([Wg.view(-1, 128, K), Wu.view(-1, 128, K)], dim=1).reshape(2 * inter, K).contiguous()
+    out = torch.zeros((M, inter), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(A, Wgu, out, epi_mode=pb.EPI_GEGLU, bn=256, splits=splits)
+    torch.cuda.synchronize()
+    g = _ref_linear(A, Wg).bfloat16().float()
+    u = _ref_linear(A, Wu).bfloat16().float()
+    ref = (torch.nn.functional.gelu(g, approximate="tanh").bfloat16().float() * u).bfloat16().float()
+    assert (out.float() - ref).abs().max().item() <= 3e-2 * max(1.0, ref.abs().max().item())
+
+
+def test_gemm_batched_splitk(cuda):
+    """Denoise-shaped scores: 40 query rows x 333 keys per sample, batched over samples, K = 256 split in two."""
+    B, R, Kk, D = 6, 40, 333, 256
+    q = _rand((B, R, D), cuda, seed=41)
+    k = _rand((B, 336, D), cuda, seed=42)
+    sc = torch.zeros((B, R, 336), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(q, k, sc, M=R, N=Kk, K=D, lda=D, ldw=D, ldc=336, nz0=B, a_z=(R * D, 0), w_z=(336 * D, 0),
+            out_z=(R * 336, 0), alpha=0.0625, bn=64, splits=2)
+    torch.cuda.synchronize()
+    ref = ((q.float() @ k[:, :Kk].float().transpose(1, 2)).bfloat16().float() * 0.0625).bfloat16().float()
+    assert (sc[:, :, :Kk].float() - ref).abs().max().item() <= 3e-2 * ref.abs().max().item()
+
+
 def test_gemm_tc_throughput_report(cuda):
     """Not an assertion on speed: prints achieved TFLOP/s of the tcgen05 kernel for the log."""
     M, N, K = 8192, 8192, 2048
