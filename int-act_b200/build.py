@@ -16,7 +16,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v",
-]
+] + os.environ.get("PI0_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _sources():
@@ -26,6 +26,7 @@ def _sources():
 def _digest():
     h = hashlib.sha256()
     inc = os.path.join(os.path.dirname(HERE), "include", "pi0b200.h")
+    h.update(os.environ.get("PI0_EXTRA_NVCC_FLAGS", "").encode())
     for p in sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)) + [inc, __file__]:
         with open(p, "rb") as f:
             h.update(p.encode())

@@ -42,6 +42,44 @@ const char* get_error();
   } while (0)
 
 // ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch: every kernel of the path is launched with the programmatic-stream-serialization
+// attribute, triggers its dependents at entry and waits for its predecessor (griddepcontrol.wait = full completion +
+// memory flush of the previous grid) before it touches global memory. The launch latency and the prologue (barrier
+// init, TMEM allocation, descriptor prefetch) of kernel N+1 thereby overlap the tail of kernel N - also inside a
+// captured CUDA graph (programmatic dependency edges). PI0_PDL=0 in the environment turns it off.
+// ---------------------------------------------------------------------------------------------
+bool pdl_enabled();
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              int cluster_x, Args... args) {
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = grid;
+  lc.blockDim = block;
+  lc.dynamicSmemBytes = smem;
+  lc.stream = stream;
+  cudaLaunchAttribute at[2];
+  unsigned n = 0;
+  if (cluster_x > 1) {
+    at[n].id = cudaLaunchAttributeClusterDimension;
+    at[n].val.clusterDim.x = (unsigned)cluster_x;
+    at[n].val.clusterDim.y = 1;
+    at[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  lc.attrs = at;
+  lc.numAttrs = n;
+  return cudaLaunchKernelEx(&lc, kernel, args...);
+}
+
+// ---------------------------------------------------------------------------------------------
 // numeric helpers
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }

@@ -54,6 +54,8 @@ __device__ __forceinline__ float block_max(float v, float* red) {
 template <typename T>
 __global__ void im2col_patch_kernel(const float* __restrict__ img, T* __restrict__ out, int B, int kpad, float scale,
                                     float shift) {
+  pdl_trigger();
+  pdl_wait();
   const int patch = blockIdx.x;            // b*256 + py*16 + px
   const int b = patch >> 8, pp = patch & 255;
   const int py = pp >> 4, px = pp & 15;
@@ -71,7 +73,7 @@ __global__ void im2col_patch_kernel(const float* __restrict__ img, T* __restrict
 }
 template <typename T>
 int im2col_patch(const float* img, T* out, int B, int kpad, float scale, float shift, cudaStream_t s) {
-  im2col_patch_kernel<T><<<B * 256, 128, 0, s>>>(img, out, B, kpad, scale, shift);
+  PI0_CHECK_CUDA(launch_pdl(im2col_patch_kernel<T>, dim3(B * 256), dim3(128), 0, s, 1, img, out, B, kpad, scale, shift));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -84,6 +86,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) layernorm_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                         const float* __restrict__ w, const float* __restrict__ bias,
                                                         int D, float eps) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[8];
   const int64_t row = blockIdx.x;
   const T* xr = x + row * D;
@@ -109,6 +113,8 @@ template <typename T, int NCH>
 __global__ void __launch_bounds__(256) layernorm_warp_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                              const float* __restrict__ w,
                                                              const float* __restrict__ bias, int M, int D, float eps) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= M) return;
   const int lane = threadIdx.x & 31;
@@ -152,9 +158,9 @@ __global__ void __launch_bounds__(256) layernorm_warp_kernel(const T* __restrict
 template <typename T>
 int layernorm(const T* x, T* y, const float* w, const float* b, int M, int D, float eps, cudaStream_t s) {
   if (D % 8 == 0 && D <= 32 * 8 * 5) {
-    layernorm_warp_kernel<T, 5><<<(M + 7) / 8, 256, 0, s>>>(x, y, w, b, M, D, eps);
+    PI0_CHECK_CUDA(launch_pdl(layernorm_warp_kernel<T, 5>, dim3((M + 7) / 8), dim3(256), 0, s, 1, x, y, w, b, M, D, eps));
   } else {
-    layernorm_kernel<T><<<M, 256, 0, s>>>(x, y, w, b, D, eps);
+    PI0_CHECK_CUDA(launch_pdl(layernorm_kernel<T>, dim3(M), dim3(256), 0, s, 1, x, y, w, b, D, eps));
   }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
@@ -169,6 +175,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) rmsnorm_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                       const float* __restrict__ g, int D, float eps, int rpb_in,
                                                       int rpb_out, int off) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[8];
   const int r = blockIdx.x;
   const int64_t in_row = rpb_in > 0 ? (int64_t)(r / rpb_in) * rpb_out + off + (r % rpb_in) : r;
@@ -195,6 +203,8 @@ template <typename T, int NCH>
 __global__ void __launch_bounds__(256) rmsnorm_warp_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                            const float* __restrict__ g, int M, int D, float eps,
                                                            int rpb_in, int rpb_out, int off) {
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (r >= M) return;
   const int lane = threadIdx.x & 31;
@@ -229,9 +239,9 @@ template <typename T>
 int rmsnorm(const T* x, T* y, const float* g, int M, int D, float eps, int rpb_in, int rpb_out, int off,
             cudaStream_t s) {
   PI0_REQUIRE(D % 8 == 0, "rmsnorm: D=%d must be a multiple of 8", D);
-  if (D <= 1024) rmsnorm_warp_kernel<T, 4><<<(M + 7) / 8, 256, 0, s>>>(x, y, g, M, D, eps, rpb_in, rpb_out, off);
-  else if (D <= 2048) rmsnorm_warp_kernel<T, 8><<<(M + 7) / 8, 256, 0, s>>>(x, y, g, M, D, eps, rpb_in, rpb_out, off);
-  else rmsnorm_kernel<T><<<M, 256, 0, s>>>(x, y, g, D, eps, rpb_in, rpb_out, off);
+  if (D <= 1024) PI0_CHECK_CUDA(launch_pdl(rmsnorm_warp_kernel<T, 4>, dim3((M + 7) / 8), dim3(256), 0, s, 1, x, y, g, M, D, eps, rpb_in, rpb_out, off));
+  else if (D <= 2048) PI0_CHECK_CUDA(launch_pdl(rmsnorm_warp_kernel<T, 8>, dim3((M + 7) / 8), dim3(256), 0, s, 1, x, y, g, M, D, eps, rpb_in, rpb_out, off));
+  else PI0_CHECK_CUDA(launch_pdl(rmsnorm_kernel<T>, dim3(M), dim3(256), 0, s, 1, x, y, g, D, eps, rpb_in, rpb_out, off));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -250,6 +260,8 @@ __global__ void __launch_bounds__(256) softmax_kernel(T* __restrict__ sc, int64_
                                                       int64_t pitch, int n_keys, int n_prefix,
                                                       const uint8_t* __restrict__ pad, int pad_pitch,
                                                       const int* __restrict__ cum, int heads) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows_total) return;
   const int lane = threadIdx.x & 31;
@@ -293,6 +305,8 @@ __global__ void __launch_bounds__(256) softmax_warp_kernel(T* __restrict__ sc, i
                                                            int64_t pitch, int n_keys, int n_prefix,
                                                            const uint8_t* __restrict__ pad, int pad_pitch,
                                                            const int* __restrict__ cum, int heads) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows_total) return;
   const int lane = threadIdx.x & 31;
@@ -360,15 +374,15 @@ int softmax_rows(T* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n
                       (pad == nullptr || pad_pitch % 8 == 0) && (n_keys == n_prefix ? n_keys % 8 == 0 : cum != nullptr) &&
                       (reinterpret_cast<uintptr_t>(sc) % 32 == 0) &&
                       (pad == nullptr || reinterpret_cast<uintptr_t>(pad) % 8 == 0);
-#define PI0_SM(NCH) softmax_warp_kernel<T, NCH><<<(unsigned)blocks, 256, 0, s>>>(sc, rows_total, rows_per_b, pitch, \
-                                                 n_keys, n_prefix, pad, pad_pitch, cum, heads)
+#define PI0_SM(NCH) PI0_CHECK_CUDA(launch_pdl(softmax_warp_kernel<T, NCH>, dim3((unsigned)blocks), dim3(256), 0, s, 1, \
+                                              sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads))
   if (vec_ok && n_keys <= 256) PI0_SM(1);
   else if (vec_ok && n_keys <= 512) PI0_SM(2);
   else if (vec_ok && n_keys <= 768) PI0_SM(3);
   else if (vec_ok && n_keys <= 1024) PI0_SM(4);
   else
-    softmax_kernel<T><<<(unsigned)blocks, 256, 0, s>>>(sc, rows_total, rows_per_b, pitch, n_keys, n_prefix, pad,
-                                                       pad_pitch, cum, heads);
+    PI0_CHECK_CUDA(launch_pdl(softmax_kernel<T>, dim3((unsigned)blocks), dim3(256), 0, s, 1, sc, rows_total, rows_per_b,
+                              pitch, n_keys, n_prefix, pad, pad_pitch, cum, heads));
 #undef PI0_SM
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
@@ -382,6 +396,8 @@ int softmax_rows(T* sc, int64_t rows_total, int rows_per_b, int64_t pitch, int n
 template <typename T>
 __global__ void embed_tokens_kernel(const int64_t* __restrict__ tok, const T* __restrict__ table, T* __restrict__ out,
                                     int L, int P, int row_off, int D, int64_t vocab, float scale) {
+  pdl_trigger();
+  pdl_wait();
   const int bt = blockIdx.x;
   const int b = bt / L, t = bt % L;
   int64_t id = tok[bt];
@@ -400,7 +416,7 @@ __global__ void embed_tokens_kernel(const int64_t* __restrict__ tok, const T* __
 template <typename T>
 int embed_tokens(const int64_t* tok, const T* table, T* out, int B, int L, int P, int row_off, int D, int64_t vocab,
                  float scale, cudaStream_t s) {
-  embed_tokens_kernel<T><<<B * L, 256, 0, s>>>(tok, table, out, L, P, row_off, D, vocab, scale);
+  PI0_CHECK_CUDA(launch_pdl(embed_tokens_kernel<T>, dim3(B * L), dim3(256), 0, s, 1, tok, table, out, L, P, row_off, D, vocab, scale));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -412,6 +428,8 @@ int embed_tokens(const int64_t* tok, const T* table, T* out, int B, int L, int P
 // ---------------------------------------------------------------------------------------------
 __global__ void position_ids_kernel(const uint8_t* __restrict__ pad, int P, int S, int* __restrict__ prefix_pos,
                                     int* __restrict__ suffix_pos) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   if (threadIdx.x == 0) {
     int c = 0;
@@ -423,7 +441,7 @@ __global__ void position_ids_kernel(const uint8_t* __restrict__ pad, int P, int 
   }
 }
 int position_ids(const uint8_t* pad, int B, int P, int S, int* prefix_pos, int* suffix_pos, cudaStream_t s) {
-  position_ids_kernel<<<B, 32, 0, s>>>(pad, P, S, prefix_pos, suffix_pos);
+  PI0_CHECK_CUDA(launch_pdl(position_ids_kernel, dim3(B), dim3(32), 0, s, 1, pad, P, S, prefix_pos, suffix_pos));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -432,6 +450,8 @@ int position_ids(const uint8_t* pad, int B, int P, int S, int* prefix_pos, int* 
 // build the [B, P] pad mask from per-camera image masks and the language mask (modeling_mvla.py:603-619)
 __global__ void build_pad_kernel(const uint8_t* __restrict__ img_masks, const uint8_t* __restrict__ lang_masks,
                                  uint8_t* __restrict__ pad, int B, int ncam, int L) {
+  pdl_trigger();
+  pdl_wait();
   const int P = ncam * 256 + L;
   const int b = blockIdx.x;
   for (int j = threadIdx.x; j < P; j += blockDim.x) {
@@ -443,7 +463,7 @@ __global__ void build_pad_kernel(const uint8_t* __restrict__ img_masks, const ui
 }
 int build_pad(const uint8_t* img_masks, const uint8_t* lang_masks, uint8_t* pad, int B, int ncam, int L,
               cudaStream_t s) {
-  build_pad_kernel<<<B, 128, 0, s>>>(img_masks, lang_masks, pad, B, ncam, L);
+  PI0_CHECK_CUDA(launch_pdl(build_pad_kernel, dim3(B), dim3(128), 0, s, 1, img_masks, lang_masks, pad, B, ncam, L));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
@@ -452,12 +472,14 @@ int build_pad(const uint8_t* img_masks, const uint8_t* lang_masks, uint8_t* pad,
 // fp32 -> activation type (x_t and state enter the Linear layers in the activation type under autocast)
 template <typename T>
 __global__ void cast_kernel(const float* __restrict__ in, T* __restrict__ out, int64_t n) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) Num<T>::st(out + i, in[i]);
 }
 template <typename T>
 int cast_f32(const float* in, T* out, int64_t n, cudaStream_t s) {
-  cast_kernel<T><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, out, n);
+  PI0_CHECK_CUDA(launch_pdl(cast_kernel<T>, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, 1, in, out, n));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;

@@ -1,6 +1,8 @@
 // Thread-local error message behind pi0_last_error(); every C-ABI entry returns 0 or a negative code.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -15,5 +17,14 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PI0_PDL");
+    v = (e != nullptr && strcmp(e, "0") == 0) ? 0 : 1;
+  }
+  return v == 1;
+}
 
 }  // namespace pi0

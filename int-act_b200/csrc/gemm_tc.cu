@@ -11,6 +11,15 @@
 
 namespace pi0 {
 
+// Optional in-kernel timeline (development aid, compiled in with -DPI0_TIMELINE): CTA 0 stamps %globaltimer at the
+// phases of one launch; pi0_debug_timeline() copies the stamps back.
+#ifdef PI0_TIMELINE
+__device__ unsigned long long g_timeline[16];
+#define PI0_STAMP(i) do { if (blockIdx.x == 0) g_timeline[i] = global_timer_ns(); } while (0)
+#else
+#define PI0_STAMP(i) do { } while (0)
+#endif
+
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGroupM = 8;
@@ -33,6 +42,7 @@ struct TcShape {
   int total_tiles;
   int splits;        // split-K: CTAs (= cluster size) per output tile, 1 = none
   int kb_per_split;  // k-blocks (of kBK) per split
+  uint32_t stage_tx; // bytes one pipeline stage receives: A box (rows clipped to M for a single short M tile) + W box
 };
 
 __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, int& tm, int& tn) {
@@ -63,8 +73,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_trigger();
 
   if (threadIdx.x == 0) {
+#ifdef PI0_TIMELINE
+    if (blockIdx.x == 0) g_timeline[8] = g_timeline[7];
+#endif
+    PI0_STAMP(0);
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < Cfg::kStages; ++s) {
@@ -83,10 +98,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int num_k = (sh.K + kBK - 1) / kBK;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched only below
+  if (threadIdx.x == 0) PI0_STAMP(1);
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
@@ -94,12 +111,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tile_coords(sh, idx, z, tm, tn);
         const int z0 = z % sh.nz0, z1 = z / sh.nz0;
         for (int kb = 0; kb < num_k; ++kb) {
+#ifdef PI0_TIMELINE
+          long long c0 = clock64();
+#endif
           mbar_wait(&empty_bar[stage], phase ^ 1);
+#ifdef PI0_TIMELINE
+          long long c1 = clock64();
+#endif
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
+#ifdef PI0_TIMELINE
+          long long c2 = clock64();
+#endif
           tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
+#ifdef PI0_TIMELINE
+          long long c3 = clock64();
+#endif
           tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+#ifdef PI0_TIMELINE
+          long long c4 = clock64();
+          if (blockIdx.x == 0 && idx == 0 && kb == 2) {
+            g_timeline[14] = (unsigned long long)(((c1 - c0) << 48) | ((c2 - c1) << 32) | ((c3 - c2) << 16) | (c4 - c3));
+          }
+#endif
+          if (idx == (int)blockIdx.x && kb == 0) PI0_STAMP(2);
+          if (idx == (int)blockIdx.x && kb == Cfg::kStages - 1) PI0_STAMP(13);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -116,19 +153,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
       for (int kb = 0; kb < num_k; ++kb) {
+#ifdef PI0_TIMELINE
+        long long m0 = clock64();
+#endif
         mbar_wait(&full_bar[stage], phase);
+#ifdef PI0_TIMELINE
+        long long m1 = clock64();
+#endif
         tc_fence_after();
-        if (lane == 0) {
+#ifdef PI0_TIMELINE
+        long long m2 = clock64();
+#endif
+        if (elect_one()) {
+          if (idx == (int)blockIdx.x && kb == 0) PI0_STAMP(3);
+          if (idx == (int)blockIdx.x && kb == 8) PI0_STAMP(9);
+          if (idx == (int)blockIdx.x && kb == 16) PI0_STAMP(10);
+          if (idx == (int)blockIdx.x && kb == 32) PI0_STAMP(11);
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint64_t da = umma_desc_k_sw128(sa);
           const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
+#ifdef PI0_EXP_ONE_MMA
+#pragma unroll
+          for (int k = 0; k < 1; ++k) {
+#else
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
+#endif
             // advancing 16 bf16 (32 B) along K inside the 128 B swizzle row: +2 in the (>>4) address field
             umma_bf16(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
           }
+#ifdef PI0_TIMELINE
+          long long m3 = clock64();
+#endif
           umma_commit(&empty_bar[stage]);
-          if (kb == num_k - 1) umma_commit(&tfull_bar[acc]);
+#ifdef PI0_TIMELINE
+          long long m4 = clock64();
+          if (blockIdx.x == 0 && idx == 0 && kb == 20) {
+            g_timeline[15] = (unsigned long long)(((m1 - m0) << 48) | ((m2 - m1) << 32) | ((m3 - m2) << 16) | (m4 - m3));
+          }
+#endif
+          if (kb == num_k - 1) { umma_commit(&tfull_bar[acc]); PI0_STAMP(4); }
         }
         __syncwarp();
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -149,8 +213,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int row = tm * kBM + quad * 32 + lane;
       const int n0 = tn * BN;
       const bool row_ok = row < sh.M;
+#ifdef PI0_TIMELINE
+      if (threadIdx.x == 64 && idx == (int)blockIdx.x && num_k >= Cfg::kStages) {
+        mbar_wait(&full_bar[Cfg::kStages - 1], 0);  // when does the LAST stage of the first ring pass land?
+        PI0_STAMP(12);
+      }
+      __syncwarp();
+#endif
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
+      if (threadIdx.x == 64) PI0_STAMP(5);
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
 
       if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
@@ -196,6 +268,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (threadIdx.x == 64) PI0_STAMP(6);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
@@ -204,6 +277,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  if (threadIdx.x == 32) PI0_STAMP(7);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -233,7 +307,10 @@ __device__ __forceinline__ float dsmem_ld_f32(uint32_t addr) {
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
   return v;
 }
-// v[j] = sum over ranks (ascending) of partial[rank][chunk*32 + j][r]
+// Partial tiles live column-major ([col][row], 128 rows) in shared memory: the lanes of a warp own consecutive rows,
+// so both the spill and the remote reads are 128-byte coalesced (a row-major layout with 16-byte remote loads was
+// measured 2x slower: lanes then stride a whole row). v[j] = sum over ranks (ascending) of partial[rank][chunk*32+j][r].
+template <int BN>
 __device__ __forceinline__ void splitk_fetch(uint32_t stage_u32, int splits, int chunk, int r, float* v) {
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = 0.0f;
@@ -262,6 +339,7 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int splits = sh.splits;
   const int rank = (int)cluster_ctarank();
   const int tile = blockIdx.x / splits;
+  pdl_trigger();
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -281,19 +359,20 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int num_k = (sh.K + kBK - 1) / kBK;
   const int kb0 = rank * sh.kb_per_split;
   const int kb1 = min(num_k, kb0 + sh.kb_per_split);
+  pdl_wait();
   int z, tm, tn;
   tile_coords(sh, tile, z, tm, tn);
   const int z0 = z % sh.nz0, z1 = z / sh.nz0;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
         tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
         tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -306,7 +385,7 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     for (int kb = kb0; kb < kb1; ++kb) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
         const uint64_t da = umma_desc_k_sw128(sa);
         const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
@@ -358,7 +437,7 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const int col0 = n0 + c * 32;
           if (col0 >= sh.N) break;
           float v[32];
-          splitk_fetch(stage_u32, splits, c, r, v);
+          splitk_fetch<BN>(stage_u32, splits, c, r, v);
           if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
           else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
         }
@@ -370,8 +449,8 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const int out_col0 = tn * (BN / 2) + c * 32;
           if (out_col0 >= n_out) break;
           float g[32], u[32];
-          splitk_fetch(stage_u32, splits, c, r, g);
-          splitk_fetch(stage_u32, splits, BN / 64 + c, r, u);
+          splitk_fetch<BN>(stage_u32, splits, c, r, g);
+          splitk_fetch<BN>(stage_u32, splits, BN / 64 + c, r, u);
           epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
         }
       } else if constexpr (EPI == EPI_ROPE) {
@@ -381,8 +460,8 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         for (int c = rank; c < 4; c += splits, ++i) {
           if ((i & 1) != half) continue;
           float x1[32], x2[32];
-          splitk_fetch(stage_u32, splits, c, r, x1);
-          splitk_fetch(stage_u32, splits, 4 + c, r, x2);
+          splitk_fetch<BN>(stage_u32, splits, c, r, x1);
+          splitk_fetch<BN>(stage_u32, splits, 4 + c, r, x2);
           epi_rope_chunk<bf16>(ep, row, which, tn, c, x1, x2);
         }
       }
@@ -448,7 +527,10 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
     attr_set = true;
   }
   CUtensorMap tmA, tmB;
-  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, kBM));
+  // a single short M tile only fetches the rows that exist (rounded to the 8-row swizzle atom): the MMA still reads
+  // 128 smem rows, but rows >= M only feed accumulator rows that the epilogue never stores
+  const int a_rows = g.M < kBM ? ((g.M + 7) / 8) * 8 : kBM;
+  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, a_rows));
   PI0_TRY(make_map(&tmB, g.W, g.K, g.N, g.nz0, g.nz1, g.ldw, g.w_z0, g.w_z1, BN));
   TcShape sh;
   sh.M = g.M; sh.N = g.N; sh.K = g.K; sh.nz0 = g.nz0; sh.nz1 = g.nz1;
@@ -458,6 +540,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   const int num_k = (g.K + kBK - 1) / kBK;
   sh.splits = 1;
   sh.kb_per_split = num_k;
+  sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
   if (splits > 1) {
     // every rank of the cluster must own at least one k-block
     int per = (num_k + splits - 1) / splits;
@@ -466,49 +549,86 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
     sh.kb_per_split = per;
   }
   if (sh.splits > 1) {
-    cudaLaunchConfig_t lc = {};
-    lc.gridDim = dim3((unsigned)(sh.total_tiles * sh.splits), 1, 1);
-    lc.blockDim = dim3(kTcThreads, 1, 1);
-    lc.dynamicSmemBytes = Cfg::kSmemBytes;
-    lc.stream = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = (unsigned)sh.splits;
-    at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
-    lc.attrs = at;
-    lc.numAttrs = 1;
-    PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, gemm_tc_splitk_kernel<BN, EPI>, tmA, tmB, sh, g.epi));
+    PI0_CHECK_CUDA(launch_pdl(gemm_tc_splitk_kernel<BN, EPI>, dim3((unsigned)(sh.total_tiles * sh.splits)),
+                              dim3(kTcThreads), Cfg::kSmemBytes, stream, sh.splits, tmA, tmB, sh, g.epi));
   } else {
     int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
-    gemm_tc_kernel<BN, EPI><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, sh, g.epi);
+    PI0_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcThreads), Cfg::kSmemBytes, stream,
+                              1, tmA, tmB, sh, g.epi));
   }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
 }
 
-// Tile / split choice for the plain-store epilogue (bn == 0 => auto): maximise the number of busy SMs, prefer the
-// widest tile (fewest A re-reads) and the fewest splits among equals. Split factors are cluster sizes (<= 8).
+// How many clusters of `sp` GEMM CTAs (1 CTA per SM: ~195 KB of shared memory each) the device can hold at once.
+// GPCs have 16-20 SMs, so e.g. only two clusters of 8 fit a GPC; a launch that needs more runs in waves.
+int max_active_clusters(int sp, int num_sms) {
+  static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (sp <= 1) return num_sms;
+  if (cache[sp] > 0) return cache[sp];
+  using Cfg = TcCfg<256>;
+  cudaFuncSetAttribute(gemm_tc_splitk_kernel<256, EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)Cfg::kSmemBytes);
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3((unsigned)(sp * 64), 1, 1);
+  lc.blockDim = dim3(kTcThreads, 1, 1);
+  lc.dynamicSmemBytes = Cfg::kSmemBytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)sp;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  lc.attrs = at;
+  lc.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_splitk_kernel<256, EPI_STORE>, &lc) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    n = num_sms / sp > 2 ? num_sms / sp - 2 : 1;  // conservative guess
+  }
+  cache[sp] = n;
+  return n;
+}
+
+// Tile / split choice (bn == 0 / splits == 0 => auto). Cost model in microseconds, calibrated with
+// tools/small_bench.py and tools/timeline.py on a B200:
+//   t = launch gap + waves * (CTA setup/exit + k-blocks per CTA * t_kb(bn) + epilogue + split reduction)
+// One elected thread issues the TMA / tcgen05 instructions (~32 / ~65 cycles each), so a k-block costs >= ~0.21 us
+// whatever the tile width; wide tiles are MMA-bound (0.47 us per 128x256x64 k-block under the power cap). A persistent launch
+// (splits == 1) pays the CTA setup once. Split factors are thread-block cluster sizes (<= 8); every rank must own
+// >= 2 k-blocks; the reduction moves rows x 32 x 4 B per chunk and rank over distributed shared memory.
 void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* bn_io, int* splits_out) {
   const int tm = (M + kBM - 1) / kBM;
   const int num_k = (K + kBK - 1) / kBK;
+  const int rows = M < kBM ? M : kBM;
   int best_bn = fixed_bn ? *bn_io : 256, best_s = 1;
-  long best_score = -1;
+  double best_cost = 1e30;
   const int cands[4] = {256, 128, 64, 32};
+  const double t_kb[4] = {0.47, 0.35, 0.30, 0.28};       // many waves: MMA / power bound
+  const double t_kb_skinny[4] = {0.34, 0.25, 0.21, 0.21};  // one wave: issue bound
   for (int ci = 0; ci < 4; ++ci) {
     const int bn = cands[ci];
     if (fixed_bn && bn != *bn_io) continue;
-    if (!fixed_bn && bn == 32) continue;
     if (!fixed_bn && bn > 64 && N < bn) continue;
     const long tiles = (long)tm * ((N + bn - 1) / bn) * nz;
+    const double t_epi = 0.3 * bn / 64.0;
     for (int sp = 1; sp <= 8; ++sp) {
-      if (sp > 1 && (tiles * sp > num_sms || num_k / sp < 2)) break;
-      long busy = tiles * sp < num_sms ? tiles * sp : num_sms;
-      // full waves only matter once there are more tiles than SMs; a partial second wave costs a whole one
-      if (tiles > num_sms) busy = num_sms * tiles / (((tiles + num_sms - 1) / num_sms) * num_sms);
-      long score = busy * 1000 + (bn >> 5) * 8 - sp;
-      if (score > best_score) { best_score = score; best_bn = bn; best_s = sp; }
+      if (sp > 1 && num_k / sp < 2) break;
+      const int per = (num_k + sp - 1) / sp;
+      double cost;
+      if (sp == 1) {
+        const long waves = (tiles + num_sms - 1) / num_sms;
+        // a single skinny wave is issue-bound (0.37 us per k-block), many waves are MMA/power-bound
+        cost = 1.7 + 2.5 + (double)waves * per * (waves > 1 ? t_kb[ci] : t_kb_skinny[ci]) + t_epi;
+      } else {
+        const int cap = max_active_clusters(sp, num_sms);
+        const long waves = (tiles + cap - 1) / cap;
+        const int chunks = bn / 32;
+        const double red_bytes = (double)rows * 32 * 4 * sp * ((chunks + sp - 1) / sp);
+        cost = 1.7 + (double)waves * (2.5 + per * t_kb_skinny[ci] + t_epi / sp + 0.5 + red_bytes / 21000.0);
+      }
+      cost += 1e-3 * sp;
+      if (cost < best_cost) { best_cost = cost; best_bn = bn; best_s = sp; }
     }
   }
   *bn_io = best_bn;
@@ -556,3 +676,12 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
 }
 
 }  // namespace pi0
+
+// development aid (not part of the C ABI in include/pi0b200.h): cluster capacity the tile picker works with
+extern "C" int pi0_debug_max_clusters(int sp) { return pi0::max_active_clusters(sp, 148); }
+
+#ifdef PI0_TIMELINE
+extern "C" int pi0_debug_timeline(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, pi0::g_timeline, sizeof(pi0::g_timeline)) == cudaSuccess ? 0 : -1;
+}
+#endif

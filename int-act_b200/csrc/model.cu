@@ -161,6 +161,8 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
 }
 
 __global__ void suffix_cum_kernel(int* cum, int S) {
+  pdl_trigger();
+  pdl_wait();
   // att_masks of the suffix = [1, 1, 0, ...] (modeling_mvla.py:686-692) => cumsum = [1, 2, 2, ...]
   for (int i = threadIdx.x; i < S; i += blockDim.x) cum[i] = i == 0 ? 1 : 2;
 }
@@ -500,8 +502,7 @@ int pi0_prefill(pi0_ctx* c, int B, const uint8_t* img_masks, const uint8_t* lang
   PROF("prefill.masks_posids");
   PI0_TRY(build_pad(img_masks, lang_masks, c->pad, B, c->ncam, c->L, s));
   PI0_TRY(position_ids(c->pad, B, c->P, c->S, c->prefix_pos, c->suffix_pos, s));
-  suffix_cum_kernel<<<1, 64, 0, s>>>(c->suffix_cum, c->S);
-  PI0_CHECK_CUDA(cudaGetLastError());
+  PI0_CHECK_CUDA(launch_pdl(suffix_cum_kernel, dim3(1), dim3(64), 0, s, 1, c->suffix_cum, c->S));
   ++g_launch_count;
   }
   const int NL = c->cfg.n_gemma_layers;
