@@ -177,6 +177,11 @@ int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype,
 int pi0_layernorm(const void* x, void* y, const float* w, const float* b, int M, int D, int dtype, void* stream);
 int pi0_softmax(void* scores, int64_t rows_total, int rows_per_b, int64_t pitch, int n_keys, int n_prefix,
                 const uint8_t* pad, int pad_pitch, const int32_t* cum, int heads, int dtype, void* stream);
+/* Fused suffix attention of one denoise step (bf16): q [B*S, 8*256], K cache [B, kv_pitch, 256], V^T cache
+ * [B, 256, vt_pitch], pad u8 [B, P], cum i32 [S] (cumsum of the suffix att mask) -> att [B*S, 8*256].
+ * Replaces eager_attention_forward for the suffix ([mirror] src/model/mvla/mllm.py:265-317). */
+int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                         const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
 #ifdef __cplusplus

@@ -98,6 +98,8 @@ SIGNATURES = {
     "pi0_layernorm": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),
     "pi0_softmax": (C.c_int, [c_ptr, C.c_int64, C.c_int, C.c_int64, C.c_int, C.c_int, c_ptr, C.c_int, c_ptr,
                               C.c_int, C.c_int, c_ptr]),
+    "pi0_decode_attention": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, c_ptr]),
     "pi0_position_ids": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr]),
 }
 

@@ -61,6 +61,11 @@ int pi0_softmax(void* scores, int64_t rows_total, int rows_per_b, int64_t pitch,
                             (cudaStream_t)stream);
 }
 
+int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                         const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream) {
+  return decode_attention(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch, num_sms, (cudaStream_t)stream);
+}
+
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream) {
   return position_ids(pad, B, P, S, prefix_pos, suffix_pos, (cudaStream_t)stream);
 }

@@ -20,6 +20,10 @@ int embed_tokens(const int64_t* tok, const T* table, T* out, int B, int L, int P
 template <typename T>
 int cast_f32(const float* in, T* out, int64_t n, cudaStream_t s);
 
+// fused suffix attention of the denoise step (attn_decode.cu), bf16 only
+int decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                     const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);
+
 int position_ids(const uint8_t* pad, int B, int P, int S, int* prefix_pos, int* suffix_pos, cudaStream_t s);
 int build_pad(const uint8_t* img_masks, const uint8_t* lang_masks, uint8_t* pad, int B, int ncam, int L,
               cudaStream_t s);

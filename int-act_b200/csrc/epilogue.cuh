@@ -154,7 +154,7 @@ __device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, in
   }
   if (ep.act == ACT_GELU_TANH) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(gelu_tanh(v[j]));
+    for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(Num<T>::gelu(v[j]));
   } else if (ep.act == ACT_SILU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = Num<T>::rnd(silu(v[j]));
@@ -189,7 +189,7 @@ __device__ __forceinline__ void epi_geglu_chunk(const EpiParams& ep, int row, in
     float t[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float a = Num<T>::rnd(gelu_tanh(Num<T>::rnd(gate[g * 8 + j])));
+      float a = Num<T>::rnd(Num<T>::gelu(Num<T>::rnd(gate[g * 8 + j])));
       float u = Num<T>::rnd(up[g * 8 + j]);
       t[j] = a * u;
     }

@@ -247,6 +247,12 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   }
   if (kv_only) return 0;
 
+  if (suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && c->S <= 48 && c->P + c->S <= 640) {
+    // denoise step, bf16: scores + masked softmax + P.V in one launch over the cached prefix
+    PROF("denoise.attention");
+    PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
+                             c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+  } else {
   // scores[b, t*8+h, j] = rnd(rnd(q . k) * 256^-0.5)   (MQA: the 8 heads of a token are 8 rows against one K)
   {
     GemmProblem g = gemm_problem(q, kHd, kc, kHd, T * kHeads, n_keys, kHd);
@@ -266,6 +272,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     g.bn = 256;
     g.epi.out = att; g.epi.ldc = kHd; g.epi.out_z0 = (int64_t)T * kHeads * kHd;
     PI0_TRY(run_gemm(c, L[4], g, s));
+  }
   }
   // o_proj + residual
   {

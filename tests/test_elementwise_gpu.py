@@ -119,3 +119,39 @@ def test_position_ids_bit_exact(cuda):
     torch.cuda.synchronize()
     assert torch.equal(pp.cpu().long(), torch.cumsum(pad.long(), 1) - 1)
     assert torch.equal(sp.cpu().long(), pad.sum(1)[:, None] + torch.arange(S)[None])
+
+
+@pytest.mark.parametrize("B,S,P", [(1, 5, 328), (3, 5, 328), (70, 5, 320), (2, 17, 584), (2, 1, 64)])
+def test_decode_attention_fused(cuda, B, S, P):
+    """Fused suffix attention (scores + masked softmax + P.V in one launch) against a torch restatement with the
+    reference's rounding points ([mirror] mllm.py:265-317): bf16 scores, fp32 softmax, bf16 probabilities."""
+    g = torch.Generator().manual_seed(5)
+    n_keys = P + S
+    kv_pitch, vt_pitch = n_keys, (n_keys + 7) // 8 * 8
+    q = torch.randn((B * S, 8 * 256), generator=g).bfloat16()
+    k = torch.randn((B, kv_pitch, 256), generator=g).bfloat16()
+    v = torch.randn((B, n_keys, 256), generator=g).bfloat16()
+    vt = torch.zeros((B, 256, vt_pitch), dtype=torch.bfloat16)
+    vt[:, :, :n_keys] = v.transpose(1, 2)
+    pad = torch.ones((B, P), dtype=torch.bool)
+    pad[0, P - 37:] = False
+    if B > 1:
+        pad[1, :3] = False
+    cum = torch.tensor([1] + [2] * (S - 1), dtype=torch.int32)
+    d = lambda t: t.to(cuda)
+    att = torch.zeros((B * S, 8 * 256), dtype=torch.bfloat16, device=cuda)
+    dq, dk, dvt, dpad, dcum = d(q), d(k), d(vt), d(pad.to(torch.uint8)), d(cum)
+    pb.check(pb.lib().pi0_decode_attention(pb.ptr(dq), pb.ptr(dk), pb.ptr(dvt), pb.ptr(att), pb.ptr(dpad), pb.ptr(dcum),
+                                           B, S, P, kv_pitch, vt_pitch, 148, _stream()), "pi0_decode_attention")
+    torch.cuda.synchronize()
+    qf = q.float().view(B, S, 8, 256)
+    sc = torch.einsum("bshd,bjd->bshj", qf, k.float()).bfloat16().float()
+    sc = (sc * 0.0625).bfloat16().float()
+    mask = torch.ones((B, S, n_keys), dtype=torch.bool)
+    mask[:, :, :P] = pad[:, None, :]
+    mask[:, :, P:] = (cum[None, :] <= cum[:, None])[None]
+    sc = torch.where(mask[:, :, None, :], sc, torch.tensor(NEG))
+    pr = torch.softmax(sc, dim=-1).bfloat16().float()
+    ref = torch.einsum("bshj,bjd->bshd", pr, v.float()).bfloat16().float().reshape(B * S, 8 * 256)
+    err = (att.float().cpu() - ref).abs().max().item()
+    assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err

@@ -47,32 +47,38 @@ def run(name, M, N, K, bn, splits, epi=0, res=True):
           f"{wbytes / us / 1e3:7.1f} GB/s(W)  {2.0 * M * N * K / us / 1e6:8.1f} TFLOP/s", flush=True)
 
 
-flt = sys.argv[1] if len(sys.argv) > 1 else ""
-x = torch.zeros(64, device=dev)
-y = torch.zeros(64, device=dev, dtype=torch.bfloat16)
-print(f"floor (torch 64-elem copy kernel): {graph_time(lambda: y.copy_(x)):.2f} us/launch")
+def main():
+    flt = sys.argv[1] if len(sys.argv) > 1 else ""
+    x = torch.zeros(64, device=dev)
+    y = torch.zeros(64, device=dev, dtype=torch.bfloat16)
+    print(f"floor (torch 64-elem copy kernel): {graph_time(lambda: y.copy_(x)):.2f} us/launch")
 
-print("max active clusters by size:", {sp: pb.lib().pi0_debug_max_clusters(sp) for sp in range(2, 9)})
-cases = []
-for M in (5, 320):
-    for bn, sp in ((32, 1), (64, 1), (64, 4), (64, 8), (128, 4), (128, 6), (128, 8), (256, 4), (256, 8), (0, 0)):
-        cases.append(("exp down", M, 1024, 4096, bn, sp, 0))
-    for bn, sp in ((32, 1), (64, 8), (128, 6), (256, 8), (0, 0)):
-        cases.append(("exp o_proj", M, 1024, 2048, bn, sp, 0))
-    for bn, sp in ((256, 1), (256, 2), (256, 4), (256, 0)):
-        cases.append(("exp qkv(plain)", M, 2560, 1024, bn, sp, 0))
-    for sp in (1, 2, 4, 0):
-        cases.append(("exp gateup geglu", M, 8192, 1024, 256, sp, pb.EPI_GEGLU))
-for bn, sp in ((64, 1), (256, 4), (256, 6), (128, 2), (0, 0)):
-    cases.append(("b1 prefill down", 328, 2048, 16384, bn, sp, 0))
-for bn, sp in ((256, 1), (128, 1), (0, 0)):
-    cases.append(("b1 prefill gateup", 328, 32768, 2048, 256, sp if bn == 256 else 0, pb.EPI_GEGLU))
-for bn, sp in ((64, 1), (256, 4), (0, 0)):
-    cases.append(("b1 prefill o_proj", 328, 2048, 2048, bn, sp, 0))
-for bn, sp in ((128, 1), (256, 2), (256, 4), (0, 0)):
-    cases.append(("b1 siglip fc1", 256, 4304, 1152, bn, sp, 0))
-for bn, sp in ((64, 1), (256, 8), (128, 6), (0, 0)):
-    cases.append(("b1 siglip fc2", 256, 1152, 4304, bn, sp, 0))
-for c in cases:
-    if flt in c[0]:
-        run(*c[:6], epi=c[6])
+    print("max active clusters by size:", {sp: pb.lib().pi0_debug_max_clusters(sp) for sp in range(2, 9)})
+    cases = []
+    for M in (5, 320):
+        for bn, sp in ((32, 1), (64, 1), (64, 4), (64, 8), (128, 4), (128, 6), (128, 8), (256, 4), (256, 8), (0, 0)):
+            cases.append(("exp down", M, 1024, 4096, bn, sp, 0))
+        for bn, sp in ((32, 1), (64, 8), (128, 6), (256, 8), (0, 0)):
+            cases.append(("exp o_proj", M, 1024, 2048, bn, sp, 0))
+        for bn, sp in ((256, 1), (256, 2), (256, 4), (256, 0)):
+            cases.append(("exp qkv(plain)", M, 2560, 1024, bn, sp, 0))
+        for sp in (1, 2, 4, 0):
+            cases.append(("exp gateup geglu", M, 8192, 1024, 256, sp, pb.EPI_GEGLU))
+    for bn, sp in ((64, 1), (256, 4), (256, 6), (128, 2), (0, 0)):
+        cases.append(("b1 prefill down", 328, 2048, 16384, bn, sp, 0))
+    for bn, sp in ((256, 1), (128, 1), (0, 0)):
+        cases.append(("b1 prefill gateup", 328, 32768, 2048, 256, sp if bn == 256 else 0, pb.EPI_GEGLU))
+    for bn, sp in ((64, 1), (256, 4), (0, 0)):
+        cases.append(("b1 prefill o_proj", 328, 2048, 2048, bn, sp, 0))
+    for bn, sp in ((128, 1), (256, 2), (256, 4), (0, 0)):
+        cases.append(("b1 siglip fc1", 256, 4304, 1152, bn, sp, 0))
+    for bn, sp in ((64, 1), (256, 8), (128, 6), (0, 0)):
+        cases.append(("b1 siglip fc2", 256, 1152, 4304, bn, sp, 0))
+    for c in cases:
+        if flt in c[0]:
+            run(*c[:6], epi=c[6])
+
+
+
+if __name__ == "__main__":
+    main()
