@@ -24,6 +24,16 @@ int cast_f32(const float* in, T* out, int64_t n, cudaStream_t s);
 int decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
                      const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);
 
+// weight-streaming mma.sync GEMMs for M <= 16 suffix rows (gemm_skinny.cu), bf16 only
+bool skinny_supported(int M);
+int skinny_qkv_rope(const void* x, int64_t ldx, const float* gain, const void* wqkv, int M, int K, void* q,
+                    const float* rope_cos, const float* rope_sin, const int* pos_ids, void* kcache, void* vtcache, int S,
+                    int P, int64_t kv_pitch, int64_t vt_pitch, cudaStream_t s);
+int skinny_linear_res(const void* A, int64_t lda, const void* W, int M, int N, int K, const void* res, int64_t ldr,
+                      void* out, int64_t ldc, cudaStream_t s);
+int skinny_gateup_geglu(const void* y, int64_t ldy, const float* gain, const void* wgu, int M, int K, int inter, void* out,
+                        int64_t ldc, cudaStream_t s);
+
 int position_ids(const uint8_t* pad, int B, int P, int S, int* prefix_pos, int* suffix_pos, cudaStream_t s);
 int build_pad(const uint8_t* img_masks, const uint8_t* lang_masks, uint8_t* pad, int B, int ncam, int L,
               cudaStream_t s);

@@ -231,6 +231,34 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   void* kc = at(c->kcache, (int64_t)layer * c->maxB * c->kv_pitch * kHd, es);
   void* vt = at(c->vtcache, (int64_t)layer * c->maxB * kHd * c->vt_pitch, es);
 
+  // latency regime (batch 1-3): weight-streaming mma.sync kernels with the norms fused in, see gemm_skinny.cu
+  if (suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && skinny_supported(M) && c->S <= 48 &&
+      c->P + c->S <= 640) {
+    {
+      PROF(L[1]);
+      PI0_TRY(skinny_qkv_rope(io.x_in, hidden, w.g1, w.wqkv, M, hidden, q, c->w.rope_cos, c->w.rope_sin, c->suffix_pos,
+                              kc, vt, c->S, c->P, c->kv_pitch, c->vt_pitch, s));
+    }
+    {
+      PROF("denoise.attention");
+      PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
+                               c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+    }
+    {
+      PROF(L[5]);
+      PI0_TRY(skinny_linear_res(att, kHidden, w.wo, M, hidden, kHidden, io.x_in, hidden, io.y, hidden, s));
+    }
+    {
+      PROF(L[7]);
+      PI0_TRY(skinny_gateup_geglu(io.y, hidden, w.g2, w.wgu, M, hidden, inter, act, inter, s));
+    }
+    {
+      PROF(L[8]);
+      PI0_TRY(skinny_linear_res(act, inter, w.wdown, M, hidden, inter, io.y, hidden, io.x_out, hidden, s));
+    }
+    return 0;
+  }
+
   // input RMSNorm
   PI0_TRY(run_rmsnorm(c, L[0], io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
 
