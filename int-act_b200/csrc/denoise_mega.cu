@@ -1,0 +1,641 @@
+// Persistent kernel for the latency regime of the denoise loop: ALL 18 action-expert layers of one Euler step in ONE
+// cooperative launch (M = B * S <= 16 suffix rows, i.e. batch 1-3 at the bridge shapes).
+//
+// Why: at batch 1 a denoise step is 623 MB of expert weights against ~10 KB of activations. As ~90 separate kernels
+// (5 per layer) every launch pays drain + launch + ramp-up and the HBM stream stops at every kernel boundary; measured
+// 40 us per layer against 5.3 us of pure weight streaming. Here one CTA per SM stays resident for the whole step:
+//   * warp 8 of every CTA is a PRODUCER that streams the CTA's share of the weights through a shared-memory ring with
+//     1-D bulk TMA copies (cp.async.bulk, 8 weight rows x 1024 k per 16 KB chunk, L2 evict-first). It runs ahead of the
+//     consumers by the depth of the ring and is never blocked by a grid barrier, so HBM keeps streaming while the
+//     consumers synchronise;
+//   * warps 0-7 are CONSUMERS: per phase they stage the (tiny) activation operand in shared memory (GemmaRMSNorm fused
+//     into the staging), run mma.sync m16n8k16 over the chunks as they land (the 8 warps split K; the k index is
+//     permuted identically on both operands so a lane's 8 consecutive k feed two MMAs), reduce across warps in a
+//     fixed order and apply the epilogue (RoPE + in-place K / V^T cache write, residual add, GeGLU);
+//   * phases of a layer: qkv+rope | attention | o_proj+res | gate/up GeGLU | down+res, separated by a grid barrier
+//     (sense-reversing counter in global memory, self-resetting => CUDA-graph replay needs no memset).
+// Work units (8 output columns over the whole K) are dealt to the CTAs by a host-built table that balances the bytes
+// every CTA streams per layer.
+// Reference arithmetic: [mirror] src/model/mvla/expert.py:128-179,387-409; mllm.py:30-53,265-317 (rounding points of
+// SURVEY.md 9.7, identical to gemm_skinny.cu / attn_decode.cu which this kernel replaces for M <= 16).
+#include <algorithm>
+#include <vector>
+
+#include "attn_decode.cuh"
+#include "denoise_mega.cuh"
+
+namespace pi0 {
+
+namespace {
+
+constexpr int kThreads = 288;                   // 8 consumer warps + 1 producer warp
+constexpr int kChunkK = 1024;                   // k elements per streamed chunk
+constexpr int kRowPitch = kChunkK + 32;         // bf16 elements; 2112 B = 64 mod 128 (conflict-free 16-byte loads)
+constexpr int kSlotBytes = 8 * kRowPitch * 2;   // 16896
+constexpr int kAK = 4096;                       // largest K (down projection)
+constexpr int kAPitch = kAK + 32;               // 8256 B = 64 mod 128
+constexpr int kHidden = 1024, kInter = 4096, kQDim = 2048;
+constexpr int kMegaKeyChunks = 12;              // keys (padded to 32) / 32 the attention phases hold in registers
+
+// Optional in-kernel timeline (development aid, -DPI0_TIMELINE): one CTA stamps %globaltimer at the phase boundaries
+// of layer 1; pi0_debug_mega_timeline() copies the stamps back.
+#ifdef PI0_TIMELINE
+__device__ unsigned long long g_mega_tl[4][32];
+#define MEGA_STAMP(i) do { if (layer == 1 && threadIdx.x == 0 && (cta == 0 || cta == 7 || cta == 64 || cta == 140)) \
+  g_mega_tl[cta == 0 ? 0 : cta == 7 ? 1 : cta == 64 ? 2 : 3][i] = global_timer_ns(); } while (0)
+#else
+#define MEGA_STAMP(i) do { } while (0)
+#endif
+
+template <bool M16>
+struct MegaCfg {
+  static constexpr int kRows = M16 ? 16 : 8;
+  static constexpr int kSlots = M16 ? 4 : 8;
+  static constexpr int kRingBytes = kSlots * kSlotBytes;
+  static constexpr int kABytes = kRows * kAPitch * 2;
+  static constexpr int kRedBytes = 2 * 8 * 2 * 16 * 8 * 4;  // [parity][warp][acc][row][col] fp32
+  static constexpr int kSmem = kRingBytes + kABytes + kRedBytes + 256 + 128;
+};
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Grid barrier over the consumer warps of all CTAs: one monotonic 64-bit arrival counter, never reset (so a CUDA-graph
+// replay needs no memset and the last arriver has no reset-then-release chain): barrier number k of a launch is passed
+// once count >= base + k * G, where base = the counter at launch start rounded down to a multiple of G (a CTA that
+// starts late sees at most G - 1 arrivals of barrier 1 on top of base). One fire-and-forget red.release per CTA and
+// one ld.acquire poll loop; the CTA-wide bar.sync on both sides extends the release / acquire to the other threads.
+// Bounded spin: a bug must surface as a launch failure, never as a hung GPU.
+struct GridBarrier {
+  unsigned long long* count;
+  unsigned long long target;  // threshold of the NEXT barrier (thread 0 only)
+  unsigned long long step;    // G
+};
+__device__ __forceinline__ void grid_barrier_init(GridBarrier& gb, unsigned long long* count, unsigned n_ctas) {
+  gb.count = count;
+  gb.step = n_ctas;
+  gb.target = 0;
+  if (threadIdx.x == 0) gb.target = (ld_acquire_u64(count) / n_ctas) * n_ctas + n_ctas;
+}
+__device__ __forceinline__ void grid_barrier(GridBarrier& gb) {
+  consumer_sync();
+  if (threadIdx.x == 0) {
+    red_release_add_u64(gb.count, 1ull);
+    if (ld_acquire_u64(gb.count) < gb.target) {
+      const uint64_t t0 = global_timer_ns();
+      uint32_t spins = 0;
+      while (ld_acquire_u64(gb.count) < gb.target) {
+        if (((++spins) & 0x3ff) == 0 && global_timer_ns() - t0 > 2000000000ull) {
+          printf("pi0: denoise grid barrier timed out (block %d)\n", blockIdx.x);
+          __trap();
+        }
+      }
+    }
+    gb.target += gb.step;
+  }
+  consumer_sync();
+}
+
+// weight row `j` (0..7) of chunk `ch` of unit `u` in phase `ph`, and the k offset of the chunk
+__device__ __forceinline__ int unit_row(int ph, int u, int ch, int j) {
+  if (ph == MEGA_QKV) return (u >> 4) * 256 + (u & 15) * 8 + ch * 128 + j;  // u = head*16 + dc; ch = RoPE half
+  if (ph == MEGA_GU) {
+    const int i = u * 8 + j;  // inter column; packed per 256 rows as 128 gate rows then the 128 matching up rows
+    return (i >> 7) * 256 + (i & 127) + ch * 128;
+  }
+  return u * 8 + j;  // o_proj / down: 8 consecutive output columns, chunks run along K
+}
+
+struct RingState {
+  int slot;
+  uint32_t phase;
+};
+
+template <bool M16>
+__device__ __forceinline__ void mma_chunk(float* acc, const bf16* As, int kc, const bf16* slot, int warp, int g,
+                                          int t4) {
+  const int k0 = warp * 128 + t4 * 8;
+#pragma unroll
+  for (int cc = 0; cc < 4; ++cc) {
+    const uint4 w = *reinterpret_cast<const uint4*>(slot + g * kRowPitch + k0 + cc * 32);
+    const uint4 lo = *reinterpret_cast<const uint4*>(As + g * kAPitch + kc * kChunkK + k0 + cc * 32);
+    uint4 hi = make_uint4(0, 0, 0, 0);
+    if constexpr (M16) hi = *reinterpret_cast<const uint4*>(As + (g + 8) * kAPitch + kc * kChunkK + k0 + cc * 32);
+    mma_bf16_16816(acc, lo.x, hi.x, lo.y, hi.y, w.x, w.y);
+    mma_bf16_16816(acc, lo.z, hi.z, lo.w, hi.w, w.z, w.w);
+  }
+}
+
+// A = rnd((x * rsqrt(mean(x^2) + eps)) * (1 + w)) for M rows of 1024 -> shared memory. Warp w normalises rows w, w + 8.
+template <bool M16>
+__device__ __forceinline__ void stage_norm(bf16* As, const bf16* x, const float* gain, int M) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int rr = 0; rr < (M16 ? 2 : 1); ++rr) {
+    const int row = warp + rr * 8;
+    if (row >= M) continue;
+    uint4 v[4];
+    float f[4][8];
+    float ss = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = ldcg_u4(x + (int64_t)row * kHidden + (i * 32 + lane) * 8);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[i]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 t = __bfloat1622float2(h[j]);
+        f[i][2 * j] = t.x;
+        f[i][2 * j + 1] = t.y;
+        ss += t.x * t.x + t.y * t.y;
+      }
+    }
+    ss = warp_sum_f(ss);
+    const float r = rsqrtf(ss / (float)kHidden + 1e-6f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = (i * 32 + lane) * 8;
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gain + k));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gain + k + 4));
+      const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      uint4 o;
+      __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        oh[j] = __floats2bfloat162_rn((f[i][2 * j] * r) * gv[2 * j], (f[i][2 * j + 1] * r) * gv[2 * j + 1]);
+      *reinterpret_cast<uint4*>(As + row * kAPitch + k) = o;
+    }
+  }
+}
+
+// plain copy of M rows x K (K multiple of 8) into the staged operand; 8 independent 16-byte loads in flight per thread
+__device__ __forceinline__ void stage_copy(bf16* As, const bf16* src, int ld, int M, int K) {
+  const int per_row = K >> 3;
+  const int total = M * per_row;
+  for (int i0 = threadIdx.x; i0 < total; i0 += 256 * 8) {
+    uint4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int i = i0 + j * 256;
+      if (i < total) {
+        const int row = i / per_row, c8 = i - row * per_row;
+        v[j] = ldcg_u4(src + (int64_t)row * ld + c8 * 8);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int i = i0 + j * 256;
+      if (i < total) {
+        const int row = i / per_row, c8 = i - row * per_row;
+        *reinterpret_cast<uint4*>(As + row * kAPitch + c8 * 8) = v[j];
+      }
+    }
+  }
+}
+
+// ---- attention of the denoise step, spread over the whole grid in two warp-granular sub-phases -------------------
+// (a) scores: unit = (sample, head, block of 16 keys); one warp computes S x 16 scores = rnd(rnd(q.k) * 256^-0.5) and
+//     stores them (bf16) to the global scratch sc[((b*8 + h)*S + t)*kp + j];
+// (b) after a grid barrier: unit = (sample, head, 128 output dims) per CTA; its warps do the masked softmax of the head's S
+//     rows (fp32, finite -2.3819763e38 mask, probabilities rounded to bf16 into a per-warp shared-memory tile) and
+//     multiplies by its 16 rows of V^T.
+// Same arithmetic and rounding points as decode_attn_body (attn_decode.cuh); only the work split differs.
+__device__ __forceinline__ void attn_scores_unit(const MegaParams& p, const bf16* kc, int u, int lane) {
+  const int g = lane >> 2, t4 = lane & 3;
+  const int n_kb = p.kp >> 4;
+  const int kb = u % n_kb, bh = u / n_kb, h = bh & 7, b = bh >> 3;
+  const int n_keys = p.P + p.S;
+  const int j0 = kb * 16;
+  int ja = j0 + g, jb = j0 + 8 + g;
+  ja = ja < n_keys ? ja : n_keys - 1;
+  jb = jb < n_keys ? jb : n_keys - 1;
+  const bf16* kbase = kc + (int64_t)b * p.kv_pitch * 256;
+  const bf16* qlo = p.q + ((int64_t)(b * p.S + g) * 8 + h) * 256 + t4 * 8;
+  const bf16* qhi = p.q + ((int64_t)(b * p.S + g + 8) * 8 + h) * 256 + t4 * 8;
+  const bool lo_ok = g < p.S, hi_ok = g + 8 < p.S;
+  float acc[2][4];
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc[nt][e] = 0.0f;
+#pragma unroll
+  for (int c0 = 0; c0 < 8; c0 += 4) {  // two rounds of 16 independent 16-byte loads per lane
+    uint4 ka[4], kbv[4], lo[4], hi[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      ka[c] = ldcg_u4(kbase + (int64_t)ja * 256 + (c0 + c) * 32 + t4 * 8);
+      kbv[c] = ldcg_u4(kbase + (int64_t)jb * 256 + (c0 + c) * 32 + t4 * 8);
+      lo[c] = lo_ok ? ldcg_u4(qlo + (c0 + c) * 32) : make_uint4(0, 0, 0, 0);
+      hi[c] = hi_ok ? ldcg_u4(qhi + (c0 + c) * 32) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      mma_bf16_16816(acc[0], lo[c].x, hi[c].x, lo[c].y, hi[c].y, ka[c].x, ka[c].y);
+      mma_bf16_16816(acc[0], lo[c].z, hi[c].z, lo[c].w, hi[c].w, ka[c].z, ka[c].w);
+      mma_bf16_16816(acc[1], lo[c].x, hi[c].x, lo[c].y, hi[c].y, kbv[c].x, kbv[c].y);
+      mma_bf16_16816(acc[1], lo[c].z, hi[c].z, lo[c].w, hi[c].w, kbv[c].z, kbv[c].w);
+    }
+  }
+  bf16* srow = p.sc + (int64_t)bh * p.S * p.kp;
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt) {
+    const int col = j0 + nt * 8 + t4 * 2;
+    if (lo_ok)
+      *reinterpret_cast<__nv_bfloat162*>(srow + (int64_t)g * p.kp + col) = __floats2bfloat162_rn(
+          bf16_round(acc[nt][0]) * 0.0625f, bf16_round(acc[nt][1]) * 0.0625f);
+    if (hi_ok)
+      *reinterpret_cast<__nv_bfloat162*>(srow + (int64_t)(g + 8) * p.kp + col) = __floats2bfloat162_rn(
+          bf16_round(acc[nt][2]) * 0.0625f, bf16_round(acc[nt][3]) * 0.0625f);
+  }
+}
+
+// bytes of the per-warp probability tile: 16 rows, pitch = 64 mod 128 bytes
+__host__ __device__ constexpr int attn_p_pitch_bytes(int kp) { return kp * 2 + (((kp * 2) & 127) ? 128 : 64); }
+
+// unit = (sample, head, half of the 256 output dims), executed by the 8 consumer warps of one CTA: warp w does the
+// masked softmax of rows w and w + 8 into the shared probability tile, then (after a CTA barrier) the P.V product for
+// 16 of the unit's 128 dims.
+__device__ __forceinline__ void attn_pv_unit(const MegaParams& p, const bf16* vt, uint8_t* ptile, int u, int warp,
+                                             int lane) {
+  const int g = lane >> 2, t4 = lane & 3;
+  const int dq = u & 3, bh = u >> 2, h = bh & 7, b = bh >> 3;
+  const int n_keys = p.P + p.S, kp = p.kp;
+  const int ppb = attn_p_pitch_bytes(kp);
+  const float kNeg = -2.3819763e38f;
+  const bf16* srow = p.sc + (int64_t)bh * p.S * kp;
+  // V^T fragments of the first round are independent of the softmax: issue them first
+  const int d0 = dq * 64 + warp * 8;
+  const bf16* va = vt + ((int64_t)b * 256 + d0 + g) * p.vt_pitch;
+  const int n_chunks = kp >> 5;
+  uint4 fa[kMegaKeyChunks];  // kp <= 384: the whole key range of this warp's 8 dims in one round of loads
+#pragma unroll
+  for (int cc = 0; cc < kMegaKeyChunks; ++cc) {
+    const int j = cc * 32 + t4 * 8;
+    fa[cc] = make_uint4(0, 0, 0, 0);
+    if (cc < n_chunks && j + 8 <= p.vt_pitch) fa[cc] = ldcg_u4(va + j);
+  }
+#pragma unroll
+  for (int rr = 0; rr < 2; ++rr) {
+    const int r = warp + rr * 8;
+    bf16* prow = reinterpret_cast<bf16*>(ptile + r * ppb);
+    if (r >= p.S) {
+      for (int j = lane; j < kp; j += 32) prow[j] = __float2bfloat16_rn(0.0f);
+      continue;
+    }
+    const int cq = p.cum[r];
+    float v[kMegaKeyChunks];
+    unsigned okbits = 0;
+#pragma unroll
+    for (int i = 0; i < kMegaKeyChunks; ++i) {  // all loads unconditional and independent: one L2 round trip
+      const int j = i * 32 + lane;
+      const int jc = j < kp ? j : kp - 1;
+      const unsigned short raw = __ldcg(reinterpret_cast<const unsigned short*>(srow) + (int64_t)r * kp + jc);
+      v[i] = __bfloat162float(__ushort_as_bfloat16(raw));
+      const int jp = j < p.P ? j : p.P - 1;
+      const bool okp = __ldg(p.pad + (int64_t)b * p.P + jp) != 0;
+      const int js = min(max(j - p.P, 0), p.S - 1);
+      const bool oks = __ldg(p.cum + js) <= cq;
+      if (j < n_keys && (j < p.P ? okp : oks)) okbits |= 1u << i;
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < kMegaKeyChunks; ++i) {
+      const int j = i * 32 + lane;
+      v[i] = j < n_keys ? (((okbits >> i) & 1u) ? v[i] : kNeg) : -INFINITY;
+      mx = fmaxf(mx, v[i]);
+    }
+    mx = warp_max_f(mx);
+    float sum = 0.0f;
+#pragma unroll
+    for (int i = 0; i < kMegaKeyChunks; ++i) {
+      v[i] = (i * 32 + lane < n_keys) ? expf(v[i] - mx) : 0.0f;
+      sum += v[i];
+    }
+    sum = warp_sum_f(sum);
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int i = 0; i < kMegaKeyChunks; ++i) {
+      const int j = i * 32 + lane;
+      if (j < kp) prow[j] = __float2bfloat16_rn(v[i] * inv);
+    }
+  }
+  consumer_sync();
+  float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+  for (int cc = 0; cc < kMegaKeyChunks; ++cc) {
+    if (cc < n_chunks) {
+      const int j = cc * 32 + t4 * 8;
+      const uint4 lo = *reinterpret_cast<const uint4*>(ptile + g * ppb + j * 2);
+      const uint4 hi = *reinterpret_cast<const uint4*>(ptile + (g + 8) * ppb + j * 2);
+      mma_bf16_16816(acc, lo.x, hi.x, lo.y, hi.y, fa[cc].x, fa[cc].y);
+      mma_bf16_16816(acc, lo.z, hi.z, lo.w, hi.w, fa[cc].z, fa[cc].w);
+    }
+  }
+  {
+    const int d = d0 + t4 * 2;
+    if (g < p.S)
+      *reinterpret_cast<__nv_bfloat162*>(p.att + ((int64_t)(b * p.S + g) * 8 + h) * 256 + d) =
+          __floats2bfloat162_rn(acc[0], acc[1]);
+    if (g + 8 < p.S)
+      *reinterpret_cast<__nv_bfloat162*>(p.att + ((int64_t)(b * p.S + g + 8) * 8 + h) * 256 + d) =
+          __floats2bfloat162_rn(acc[2], acc[3]);
+  }
+  consumer_sync();
+}
+
+template <bool M16>
+__global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaParams p) {
+  using Cfg = MegaCfg<M16>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint8_t* ring = smem;
+  bf16* As = reinterpret_cast<bf16*>(smem + Cfg::kRingBytes);
+  float* red = reinterpret_cast<float*>(smem + Cfg::kRingBytes + Cfg::kABytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kRingBytes + Cfg::kABytes + Cfg::kRedBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kSlots;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cta = blockIdx.x, G = gridDim.x;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < Cfg::kSlots; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 8);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_wait();
+
+  const int16_t* tab = p.units + (int64_t)cta * 4 * (kMegaMaxUnits + 1);
+  GridBarrier gb;
+  if (warp < 8) grid_barrier_init(gb, reinterpret_cast<unsigned long long*>(p.sync), (unsigned)G);
+
+  if (warp == 8) {
+    // ------------------------------ producer: stream this CTA's weight chunks in consumption order ---------------
+    const uint64_t policy = policy_evict_first();
+    int slot = 0;
+    uint32_t phase = 0;
+    for (int layer = 0; layer < p.n_layers; ++layer) {
+      const MegaLayerW& lw = p.L[layer];
+#pragma unroll 1
+      for (int ph = 0; ph < 4; ++ph) {
+        const bf16* W = ph == MEGA_QKV ? lw.wqkv : ph == MEGA_O ? lw.wo : ph == MEGA_GU ? lw.wgu : lw.wdown;
+        const int K = ph == MEGA_O ? kQDim : ph == MEGA_DOWN ? kInter : kHidden;
+        const int nch = ph == MEGA_DOWN ? 4 : 2;
+        const bool along_k = ph == MEGA_O || ph == MEGA_DOWN;
+        const int16_t* t = tab + ph * (kMegaMaxUnits + 1);
+        const int cnt = t[0];
+        for (int i = 0; i < cnt; ++i) {
+          const int u = t[1 + i];
+          for (int ch = 0; ch < nch; ++ch) {
+            mbar_wait(&empty_bar[slot], phase ^ 1);
+            if (lane == 0) mbar_arrive_expect_tx(&full_bar[slot], 8 * kChunkK * 2);
+            __syncwarp();
+            if (lane < 8) {
+              const int row = unit_row(ph, u, along_k ? 0 : ch, lane);
+              const bf16* src = W + (int64_t)row * K + (along_k ? ch * kChunkK : 0);
+              bulk_g2s(ring + slot * kSlotBytes + lane * kRowPitch * 2, src, kChunkK * 2, &full_bar[slot], policy);
+            }
+            if (++slot == Cfg::kSlots) { slot = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ------------------------------ consumers ------------------------------------------------------------------------
+  const int g = lane >> 2, t4 = lane & 3;
+  int slot = 0;
+  uint32_t phase = 0;
+  int parity = 0;  // double-buffered cross-warp reduction scratch
+
+  // runs this CTA's units of one GEMM phase; `epi(u, total)` is called by threads < 128 with row = tid >> 3, col = tid & 7
+  auto run_units = [&](int ph, auto&& epi) {
+    const int nch = ph == MEGA_DOWN ? 4 : 2;
+    const bool along_k = ph == MEGA_O || ph == MEGA_DOWN;
+    const int16_t* t = tab + ph * (kMegaMaxUnits + 1);
+    const int cnt = t[0];
+    for (int i = 0; i < cnt; ++i) {
+      const int u = t[1 + i];
+      float acc[2][4];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[a][e] = 0.0f;
+      for (int ch = 0; ch < nch; ++ch) {
+        mbar_wait(&full_bar[slot], phase);
+        const bf16* sl = reinterpret_cast<const bf16*>(ring + slot * kSlotBytes);
+        if (along_k) mma_chunk<M16>(acc[0], As, ch, sl, warp, g, t4);
+        else if (ch == 0) mma_chunk<M16>(acc[0], As, 0, sl, warp, g, t4);
+        else mma_chunk<M16>(acc[1], As, 0, sl, warp, g, t4);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[slot]);
+        if (++slot == Cfg::kSlots) { slot = 0; phase ^= 1; }
+      }
+      float* rp = red + parity * (8 * 2 * 16 * 8);
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * 16 + g) * 8 + t4 * 2) = make_float2(acc[a][0], acc[a][1]);
+        *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * 16 + g + 8) * 8 + t4 * 2) = make_float2(acc[a][2], acc[a][3]);
+      }
+      consumer_sync();
+      if (threadIdx.x < 128) {
+        const int row = threadIdx.x >> 3, col = threadIdx.x & 7;
+        if (row < p.M) {
+          float t0 = 0.0f, t1 = 0.0f;
+#pragma unroll
+          for (int w = 0; w < 8; ++w) {
+            t0 += rp[((w * 2 + 0) * 16 + row) * 8 + col];
+            t1 += rp[((w * 2 + 1) * 16 + row) * 8 + col];
+          }
+          epi(u, row, col, t0, t1);
+        }
+      }
+      parity ^= 1;
+    }
+  };
+
+  for (int layer = 0; layer < p.n_layers; ++layer) {
+    const MegaLayerW& lw = p.L[layer];
+    const bf16* x_in = layer == 0 ? p.x0 : p.x;
+    bf16* kc = p.kcache + (int64_t)layer * p.kc_layer_stride;
+    bf16* vt = p.vtcache + (int64_t)layer * p.vt_layer_stride;
+
+    // ---- phase 1: q|k|v = RMSNorm(x) . Wqkv^T, RoPE, caches ------------------------------------------------------
+    MEGA_STAMP(0);
+    if (layer > 0) grid_barrier(gb);
+    MEGA_STAMP(1);
+    stage_norm<M16>(As, x_in, lw.g1, p.M);
+    consumer_sync();
+    MEGA_STAMP(2);
+    run_units(MEGA_QKV, [&](int u, int row, int col, float t0, float t1) {
+      const int head = u >> 4, d = (u & 15) * 8 + col;
+      const float a = bf16_round(t0), b = bf16_round(t1);
+      float o1 = a, o2 = b;
+      if (head < 9) {
+        int pos = p.pos_ids[row];
+        if (pos < 0) pos = 0;
+        const float cs = __ldg(p.rope_cos + (int64_t)pos * 128 + d), sn = __ldg(p.rope_sin + (int64_t)pos * 128 + d);
+        o1 = a * cs - b * sn;
+        o2 = b * cs + a * sn;
+      }
+      const int bb = row / p.S, t = row % p.S;
+      if (head < 8) {
+        bf16* dst = p.q + (int64_t)row * kQDim + head * 256 + d;
+        dst[0] = __float2bfloat16_rn(o1);
+        dst[128] = __float2bfloat16_rn(o2);
+      } else if (head == 8) {
+        bf16* dst = kc + ((int64_t)bb * p.kv_pitch + p.P + t) * 256 + d;
+        dst[0] = __float2bfloat16_rn(o1);
+        dst[128] = __float2bfloat16_rn(o2);
+      } else {
+        bf16* dst = vt + (int64_t)bb * 256 * p.vt_pitch + p.P + t;
+        dst[(int64_t)d * p.vt_pitch] = __float2bfloat16_rn(o1);
+        dst[(int64_t)(d + 128) * p.vt_pitch] = __float2bfloat16_rn(o2);
+      }
+    });
+
+    // ---- phase 2a: scores, one warp per (sample, head, 16 keys) ---------------------------------------------------
+    MEGA_STAMP(3);
+    grid_barrier(gb);
+    MEGA_STAMP(4);
+    {
+      const int n_units = p.B * 8 * (p.kp >> 4);
+      for (int u = warp * G + cta; u < n_units; u += 8 * G) attn_scores_unit(p, kc, u, lane);
+    }
+    // ---- phase 2b: masked softmax + P.V, one warp per (sample, head, 16 dims) ----------------------------------------
+    MEGA_STAMP(15);
+    grid_barrier(gb);
+    MEGA_STAMP(16);
+    for (int u = cta; u < p.B * 32; u += G) attn_pv_unit(p, vt, reinterpret_cast<uint8_t*>(As), u, warp, lane);
+
+    // ---- phase 3: y = x + att . Wo^T -------------------------------------------------------------------------------
+    MEGA_STAMP(5);
+    grid_barrier(gb);
+    MEGA_STAMP(6);
+    stage_copy(As, p.att, kQDim, p.M, kQDim);
+    consumer_sync();
+    MEGA_STAMP(7);
+    run_units(MEGA_O, [&](int u, int row, int col, float t0, float) {
+      const int n = u * 8 + col;
+      const unsigned short xb = __ldcg(reinterpret_cast<const unsigned short*>(x_in) + (int64_t)row * kHidden + n);
+      const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(xb));
+      p.y[(int64_t)row * kHidden + n] = __float2bfloat16_rn(v);
+    });
+
+    // ---- phase 4: act = gelu_tanh(h . Wg^T) * (h . Wu^T), h = RMSNorm(y) -------------------------------------------
+    MEGA_STAMP(8);
+    grid_barrier(gb);
+    MEGA_STAMP(9);
+    stage_norm<M16>(As, p.y, lw.g2, p.M);
+    consumer_sync();
+    MEGA_STAMP(10);
+    run_units(MEGA_GU, [&](int u, int row, int col, float t0, float t1) {
+      const float gt = bf16_round(t0), up = bf16_round(t1);
+      const float act = bf16_round(gelu_tanh_fast(gt));
+      p.act[(int64_t)row * kInter + u * 8 + col] = __float2bfloat16_rn(act * up);
+    });
+
+    // ---- phase 5: x = y + act . Wdown^T ----------------------------------------------------------------------------
+    MEGA_STAMP(11);
+    grid_barrier(gb);
+    MEGA_STAMP(12);
+    stage_copy(As, p.act, kInter, p.M, kInter);
+    consumer_sync();
+    MEGA_STAMP(13);
+    run_units(MEGA_DOWN, [&](int u, int row, int col, float t0, float) {
+      const int n = u * 8 + col;
+      const unsigned short yb = __ldcg(reinterpret_cast<const unsigned short*>(p.y) + (int64_t)row * kHidden + n);
+      const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(yb));
+      p.x[(int64_t)row * kHidden + n] = __float2bfloat16_rn(v);
+    });
+    MEGA_STAMP(14);
+  }
+}
+
+}  // namespace
+
+// Deals the work units of the four GEMM phases to `G` CTAs, balanced PER PHASE (the kernel is latency- not bandwidth-
+// bound: a phase lasts as long as its busiest CTA): o_proj / down units (128 each) go to CTAs 0.. round-robin, the
+// qkv (160) and gate/up (512) units round-robin from the LAST CTA downwards, so that the CTAs with a spare unit there
+// are the ones idle in o_proj / down. Layout: [cta][phase][1 + kMegaMaxUnits] = count, unit ids.
+int mega_build_units(int G, std::vector<int16_t>& tab) {
+  PI0_REQUIRE(G >= 64 && G <= 1024, "denoise mega kernel: %d CTAs outside [64, 1024]", G);
+  const int W = kMegaMaxUnits + 1;
+  tab.assign((size_t)G * 4 * W, 0);
+  auto push = [&](int cta, int ph, int u) -> bool {
+    int16_t* t = tab.data() + ((size_t)cta * 4 + ph) * W;
+    if (t[0] >= kMegaMaxUnits) return false;
+    t[1 + t[0]] = (int16_t)u;
+    ++t[0];
+    return true;
+  };
+  bool ok = true;
+  for (int u = 0; u < kHidden / 8; ++u) ok = ok && push(u % G, MEGA_O, u) && push(u % G, MEGA_DOWN, u);
+  for (int u = 0; u < kInter / 8; ++u) ok = ok && push(G - 1 - (u % G), MEGA_GU, u);
+  for (int u = 0; u < 10 * 16; ++u) ok = ok && push(G - 1 - (u % G), MEGA_QKV, u);
+  PI0_REQUIRE(ok, "denoise mega kernel: unit table overflow");
+  return 0;
+}
+
+bool mega_supported(int M, int S, int P) { return M >= 1 && M <= 16 && S <= 16 && P + S <= 32 * kMegaKeyChunks; }
+
+int mega_denoise_layers(const MegaParams& p, int num_ctas, cudaStream_t s) {
+  PI0_REQUIRE(mega_supported(p.M, p.S, p.P), "denoise mega kernel: M=%d S=%d P=%d unsupported", p.M, p.S, p.P);
+  PI0_REQUIRE(p.n_layers >= 1 && p.n_layers <= 18, "denoise mega kernel: n_layers=%d", p.n_layers);
+  const bool m16 = p.M > 8;
+  const size_t smem = m16 ? MegaCfg<true>::kSmem : MegaCfg<false>::kSmem;
+  PI0_REQUIRE(16 * attn_p_pitch_bytes(p.kp) <= (m16 ? MegaCfg<true>::kABytes : MegaCfg<false>::kABytes) && p.kp <= 32 * kMegaKeyChunks &&
+                  p.kp % 32 == 0 && p.sc != nullptr,
+              "denoise mega kernel: attention scratch does not fit");
+  static bool attr_set = false;
+  if (!attr_set) {
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)MegaCfg<true>::kSmem));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)MegaCfg<false>::kSmem));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3((unsigned)num_ctas);
+  lc.blockDim = dim3(kThreads);
+  lc.dynamicSmemBytes = smem;
+  lc.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: the grid barrier cannot deadlock
+  at[0].val.cooperative = 1;
+  lc.attrs = at;
+  lc.numAttrs = 1;
+  if (m16) PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<true>, p));
+  else PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<false>, p));
+  ++g_launch_count;
+  return 0;
+}
+
+}  // namespace pi0
+
+#ifdef PI0_TIMELINE
+extern "C" int pi0_debug_mega_timeline(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, pi0::g_mega_tl, sizeof(pi0::g_mega_tl)) == cudaSuccess ? 0 : -1;
+}
+#endif

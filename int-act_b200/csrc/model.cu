@@ -9,6 +9,7 @@
 //   Gemma layer body    mllm.py:206-245                        attention        mllm.py:265-317
 //   embed_suffix        modeling_mvla.py:643-694               denoise_step     modeling_mvla.py:806-839
 //   Euler loop          modeling_mvla.py:787-803
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <new>
@@ -16,6 +17,7 @@
 #include <vector>
 
 #include "../../include/pi0b200.h"
+#include "denoise_mega.cuh"
 #include "elementwise.cuh"
 
 using namespace pi0;
@@ -57,6 +59,11 @@ struct pi0_ctx {
   void *suf, *xe, *ye, *he, *qe, *sc_e, *att_e, *act_e, *xt_act, *st_act, *a1, *a2, *hfin;
   uint8_t* pad;
   int *prefix_pos, *suffix_pos, *suffix_cum;
+  // persistent denoise kernel (denoise_mega.cu): per-CTA work-unit table and the grid-barrier words
+  int16_t* mega_units;
+  unsigned* mega_sync;
+  void* mega_sc;
+  int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
   Buf bufs[40];
   int nbufs;
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
@@ -154,6 +161,9 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.prefix_pos = (int*)cv.take("prefix_pos", B * P * 4);
   x.suffix_pos = (int*)cv.take("suffix_pos", B * S * 4);
   x.suffix_cum = (int*)cv.take("suffix_cum", S * 4);
+  x.mega_units = (int16_t*)cv.take("mega.units", (size_t)1024 * 4 * (kMegaMaxUnits + 1) * 2);
+  x.mega_sync = (unsigned*)cv.take("mega.sync", 64);
+  x.mega_sc = cv.take("mega.scores", (size_t)16 * 8 * 640 * 2);
   if (c) {
     c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
     c->kv_pitch = kvp; c->sc_pitch = scp; c->vt_pitch = vtp; c->es = (int)es;
@@ -365,6 +375,20 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   cv.base = c->base;
   cv.ctx = c;
   carve(cv, c, *cfg);
+  // persistent denoise kernel: deal the work units to one CTA per SM (bf16 product path only)
+  c->mega_ctas = 0;
+  const char* mega_env = getenv("PI0_MEGA");
+  const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
+  if (cfg->dtype == 0 && cfg->gemm_impl == 0 && !(mega_env && strcmp(mega_env, "0") == 0) && sms >= 64 && sms <= 1024) {
+    std::vector<int16_t> tab;
+    if (mega_build_units(sms, tab) == 0 &&
+        cudaMemcpy(c->mega_units, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice) == cudaSuccess &&
+        cudaMemset(c->mega_sync, 0, 64) == cudaSuccess) {
+      c->mega_ctas = sms;
+    } else {
+      cudaGetLastError();
+    }
+  }
   *out = c;
   return 0;
 }
@@ -592,9 +616,32 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
       g.epi.rpb_in = H; g.epi.rpb_out = S; g.epi.row_off = 1;
       PI0_TRY(run_gemm(c, "denoise.time_mlp_out", g, s));
     }
-    for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
-      LayerIO io{l == 0 ? c->suf : c->xe, c->ye, c->xe};
-      PI0_TRY(gemma_layer(c, B, l, true, io, false, s));
+    if (c->mega_ctas > 0 && mega_supported(B * S, S, c->P)) {
+      // latency regime: all expert layers of this step in one persistent cooperative launch
+      PROF("denoise.layers_mega");
+      MegaParams mp = {};
+      for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
+        const pi0_gemma_layer_w& lw = w.exp[l];
+        mp.L[l] = MegaLayerW{(const bf16*)lw.wqkv, (const bf16*)lw.wo, (const bf16*)lw.wgu, (const bf16*)lw.wdown,
+                             lw.g1, lw.g2};
+      }
+      mp.n_layers = c->cfg.n_gemma_layers;
+      mp.M = B * S; mp.S = S; mp.P = c->P; mp.B = B;
+      mp.x0 = (const bf16*)c->suf; mp.x = (bf16*)c->xe; mp.y = (bf16*)c->ye; mp.q = (bf16*)c->qe;
+      mp.att = (bf16*)c->att_e; mp.act = (bf16*)c->act_e;
+      mp.kcache = (bf16*)c->kcache; mp.vtcache = (bf16*)c->vtcache;
+      mp.kc_layer_stride = (int64_t)c->maxB * c->kv_pitch * kHd;
+      mp.vt_layer_stride = (int64_t)c->maxB * kHd * c->vt_pitch;
+      mp.kv_pitch = c->kv_pitch; mp.vt_pitch = c->vt_pitch;
+      mp.rope_cos = w.rope_cos; mp.rope_sin = w.rope_sin; mp.pos_ids = c->suffix_pos; mp.pad = c->pad;
+      mp.cum = c->suffix_cum; mp.units = c->mega_units; mp.sync = c->mega_sync;
+      mp.kp = (c->P + S + 31) / 32 * 32; mp.sc = (bf16*)c->mega_sc;
+      PI0_TRY(mega_denoise_layers(mp, c->mega_ctas, s));
+    } else {
+      for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
+        LayerIO io{l == 0 ? c->suf : c->xe, c->ye, c->xe};
+        PI0_TRY(gemma_layer(c, B, l, true, io, false, s));
+      }
     }
     // final norm on the last H rows of every sample, action_out_proj and the Euler update x_t += dt * v_t
     PI0_TRY(run_rmsnorm(c, "denoise.final_norm", c->xe, c->hfin, w.exp_norm_g, B * H, kExpHidden, H, S, 1, s));

@@ -73,7 +73,7 @@ def test_cuda_graph_replay_matches_eager_launches(cuda):
     c = e1.sample_actions(*args)  # second call = pure replay
     torch.cuda.synchronize()
     assert torch.equal(a, b) and torch.equal(b, c)
-    assert e1.launches_per_infer[3] > 100
+    assert e1.launches_per_infer[3] > 50
 
 
 def test_two_cameras_long_horizon(cuda):
