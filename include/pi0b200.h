@@ -184,6 +184,27 @@ int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache,
                          const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
+
+/* ---- environment adapters on the GPU ------------------------------------------------------------
+ * Replace, for a whole rollout batch, the per-sample host code of BridgeSimplerBatchAdapter
+ * (/root/reference/src/experiments/env_adapters/simplerMS3.py:40-132,153-172) and BridgeSimplerAdapter.postprocess
+ * (src/experiments/env_adapters/simpler.py:96-139). */
+/* images u8 [B,H,W,3] -> out f32 [B,3,out_h,out_w] = ((resize_u8(img) * rescale) - mean) / std. The resize is torch's
+ * uint8 bilinear (align_corners=False): separable, int16 fixed-point weights, uint8 rounding after each pass; the
+ * caller passes the per-axis tables idx i32 [out,2], w i16 [out,2] and their precision (simplerMS3.py:50-63). */
+int pi0_adapter_resize_normalize(const uint8_t* images, float* out, int B, int H, int W, int out_h, int out_w,
+                                 const int32_t* x_idx, const int16_t* x_w, int x_prec, const int32_t* y_idx,
+                                 const int16_t* y_w, int y_prec, float rescale, float mean, float stdv, void* stream);
+/* eef [B,8] (f32 or f64: pos | quat wxyz | gripper) -> state f32 [B,7]: quat -> R -> R.default_rot^T -> euler sxyz, then
+ * norm_type 0: bound with (p01, p99), clipped to [-1,1]; 1: gaussian with (mean, std). round_bf16 rounds f64 -> bf16
+ * like torch.as_tensor(proprio, dtype=bfloat16) (simplerMS3.py:66-88,153-165). */
+int pi0_adapter_proprio(const void* eef, int eef_is_f64, float* state, int B, const double* stat_a, const double* stat_b,
+                        int norm_type, int round_bf16, void* stream);
+/* actions f32 [N,7] -> env actions f64 [N,7]: dims 0-5 denormalised, rpy -> axis*angle, gripper 2*(g>0.5)-1
+ * (simplerMS3.py:95-132,166-172). stat_a / stat_b hold 6 entries used. */
+int pi0_adapter_postprocess(const float* actions, double* out, int N, const double* stat_a, const double* stat_b,
+                            int norm_type, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -137,6 +137,35 @@ def main():
                         obs_bytes=np.frombuffer(mnp.packb(obs), dtype=np.uint8),
                         reset_bytes=np.frombuffer(mnp.packb({"reset": True}), dtype=np.uint8),
                         status_bytes=np.frombuffer(mnp.packb({"status": "reset"}), dtype=np.uint8))
+    # ---- batch adapter (simplerMS3.py:40-132,153-172), restated call by call with the reference's own modules: the
+    # file itself cannot be imported (broken `env_adapter` import) ----------------------------------
+    import json
+    import torch.nn.functional as F
+    stats = json.load(open(f"{REF}/config/dataset/bridge_statistics.json"))
+    imgs = torch.randint(0, 256, (2, 60, 80, 3), generator=g, dtype=torch.uint8)
+    res = F.interpolate(imgs.permute(0, 3, 1, 2), size=(28, 28), mode="bilinear", align_corners=False)
+    res_full = F.interpolate(torch.randint(0, 256, (1, 480, 640, 3), generator=torch.Generator().manual_seed(7),
+                                           dtype=torch.uint8).permute(0, 3, 1, 2), size=(224, 224), mode="bilinear",
+                             align_corners=False)
+    pimgs = pipe.process_images(res, rescale_factor=1 / 255.0, image_mean=half, image_std=half)
+    eef = torch.randn(3, 8, generator=g).double().numpy()
+    eef[:, 3:7] /= np.linalg.norm(eef[:, 3:7], axis=1, keepdims=True)
+    default_rot = np.array([[0, 0, 1.0], [0, 1.0, 0], [-1.0, 0, 0]])
+    raw = np.stack([np.concatenate([p[:3], geo.mat2euler(geo.quat2mat(p[3:7]) @ default_rot.T), [p[7]]]) for p in eef])
+    state = ad.normalize_bound(raw, np.array(stats["proprio"]["p01"]), np.array(stats["proprio"]["p99"]), clip_min=-1, clip_max=1)
+    acts = (torch.rand(2, 4, 7, generator=g) * 2.4 - 1.2).numpy().astype(np.float32)
+    rex = ad.denormalize_bound(acts[:, :, :-1].astype(np.float64), np.array(stats["action"]["p01"])[:-1],
+                               np.array(stats["action"]["p99"])[:-1], clip_min=-1, clip_max=1)
+    env = np.zeros((2, 4, 7))
+    for b in range(2):
+        for t in range(4):
+            ax, ang = geo.euler2axangle(*rex[b, t, 3:6])
+            env[b, t] = np.concatenate([rex[b, t, :3], ax * ang, [2.0 * (acts[b, t, -1] > 0.5) - 1.0]])
+    np.savez_compressed(f"{OUT}/adapter_batch.npz", imgs=imgs.numpy(), resized=res.numpy(), proc=pimgs.numpy(),
+                        full_seed=np.array([7]), full_checksum=np.array([int(res_full.long().sum())]),
+                        full_corner=res_full[0, :, :4, :4].numpy(), eef=eef, raw=raw, state=state, acts=acts, env=env,
+                        p01=np.array(stats["proprio"]["p01"]), p99=np.array(stats["proprio"]["p99"]),
+                        a01=np.array(stats["action"]["p01"]), a99=np.array(stats["action"]["p99"]))
     print("golden fixtures written to", OUT)
 
 
