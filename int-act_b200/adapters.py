@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import json
 import math
+import warnings
 from types import SimpleNamespace
 from typing import Optional, Sequence
 
@@ -152,7 +153,9 @@ class BridgeSimplerBatchAdapter(_GpuAdapterBase):
 
     def preprocess(self, obs: dict) -> dict:
         frames = obs["observation.images.top"]
-        frames = torch.as_tensor(frames)
+        with warnings.catch_warnings():  # frames unpacked from the wire are read-only views; they are only read here
+            warnings.simplefilter("ignore", UserWarning)
+            frames = torch.as_tensor(frames)
         if frames.dtype != torch.uint8:
             frames = frames.to(torch.uint8)  # torch.as_tensor(..., dtype=torch.uint8), simplerMS3.py:50
         images = self.resize_normalize(frames.to(self.device, non_blocking=True))

@@ -1,0 +1,72 @@
+"""End to end through the reference-facing surface on the GPU: websocket client -> server -> LeRobotPolicyWrapper ->
+GPU batch adapter -> PI0Policy (C ABI) -> GPU post-processing -> float64 actions on the wire, checked against the same
+chain restated on the CPU (adapter oracle -> Pi0 oracle -> adapter oracle). Reduced depth (2 + 2 layers), full widths."""
+import os
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import adapters_oracle as ao
+from pi0_helpers import oracle_for
+from test_serving_cpu import ServerThread
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _build(cuda, max_batch):
+    from int_act_b200 import adapters as ad
+    from int_act_b200.config import bridge_config
+    from int_act_b200.policy import PI0Policy, SyntheticTokenizer
+    from int_act_b200.serving import LeRobotPolicyWrapper
+    from int_act_b200.weights import Dims, random_state_dict
+
+    d = np.load(os.path.join(G, "adapter_batch.npz"))
+    stats = {"proprio": {"p01": d["p01"].tolist(), "p99": d["p99"].tolist()},
+             "action": {"p01": d["a01"].tolist(), "p99": d["a99"].tolist()}}
+    dims = Dims(n_siglip_layers=2, n_gemma_layers=2, vocab=2048)
+    sd = random_state_dict(dims, device=cuda, seed=0)
+    tok = SyntheticTokenizer(dims.vocab)
+    pol = PI0Policy(bridge_config(), state_dict=sd, dims=dims, max_batch=max_batch, tokenizer=tok, device=cuda)
+    pol.to(torch.bfloat16).eval()
+    adapter = ad.BridgeSimplerBatchAdapter(ad.adapter_config("unused", use_bf16=True), dataset_statistics=stats)
+    return LeRobotPolicyWrapper(pol, adapter, action_step=4), sd, dims, stats, tok
+
+
+def _cpu_chain(sd, dims, stats, tok, frames, eef, tasks, noise):
+    imgs, state = ao.bridge_batch_preprocess(frames, eef, stats)
+    state = torch.as_tensor(state, dtype=torch.bfloat16).float()                    # adapter dtype rounding
+    ids, mask = tok([t + "\n" for t in tasks], 72)
+    orc = oracle_for(sd, dims, 1, 72, 4, "bf16")
+    B = len(tasks)
+    act = orc.infer_action([torch.from_numpy(imgs)], [torch.ones(B, dtype=torch.bool)], ids, mask, state, noise)
+    return ao.bridge_postprocess(act.float().numpy(), stats)
+
+
+def test_client_server_engine_roundtrip_matches_cpu_chain(cuda):
+    from int_act_b200.serving import WebsocketPolicyClient
+
+    wrapper, sd, dims, stats, tok = _build(cuda, max_batch=2)
+    rng = np.random.default_rng(0)
+    frames = rng.integers(0, 256, (2, 480, 640, 3), dtype=np.uint8)
+    eef = np.load(os.path.join(G, "adapter_batch.npz"))["eef"][:2].astype(np.float32)
+    tasks = ["put the carrot on the plate", "stack the green block on the yellow block"]
+    noise = torch.normal(0.0, 1.0, (2, 4, 32), generator=torch.Generator().manual_seed(42))
+    want = _cpu_chain(sd, dims, stats, tok, frames, eef, tasks, noise)
+
+    # pin the noise the policy draws (the reference draws it from the global generator inside sample_actions)
+    eng_sample = wrapper.model._ensure_engine(2).sample_actions
+    wrapper.model._ensure_engine(2).sample_actions = lambda *a, **k: eng_sample(*a[:5], noise.to(cuda)[: a[4].shape[0]])
+    with ServerThread(wrapper) as srv:
+        c = WebsocketPolicyClient("127.0.0.1", srv.bound_port)
+        assert c.reset() == {"status": "reset"}
+        got = c.infer({"observation.images.top": frames, "observation.state": eef, "task": tasks})
+        c.close()
+    assert got.dtype == np.float64 and got.shape == (2, 4, 7)
+    # translation / rotation dims: bf16 tolerance of BASELINE.json (1e-2 on the normalised action) scaled by the
+    # de-normalisation range (<= 1 here); gripper is binarised
+    assert np.abs(got[..., :3] - want[..., :3]).max() <= 1e-2
+    assert np.abs(got[..., 3:6] - want[..., 3:6]).max() <= 2e-2
+    assert np.array_equal(got[..., 6], want[..., 6])
