@@ -182,6 +182,16 @@ int pi0_softmax(void* scores, int64_t rows_total, int rows_per_b, int64_t pitch,
  * Replaces eager_attention_forward for the suffix ([mirror] src/model/mvla/mllm.py:265-317). */
 int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
                          const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream);
+/* The same attention as two wide launches for rollout batches (attn_split.cu): scores of all heads per 16-key block,
+ * then masked softmax + P.V per (sample, head, 64 dims). scratch: bf16 [B*8*S, roundup(P+S, 32)]. S <= 6, P+S <= 384.
+ * Bit-identical to pi0_decode_attention. */
+int pi0_decode_attention_split(const void* q, const void* kcache, const void* vtcache, void* att, void* scratch,
+                               const uint8_t* pad, const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch,
+                               void* stream);
+/* The same attention with one CTA per sample and the sample's K / V^T tiles staged in shared memory (attn_batch.cu):
+ * the rollout-batch path (B >= 4). S <= 6, P+S <= 352. */
+int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                               const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
 

@@ -100,6 +100,10 @@ SIGNATURES = {
                               C.c_int, C.c_int, c_ptr]),
     "pi0_decode_attention": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.c_int, c_ptr]),
+    "pi0_decode_attention_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_int, c_ptr]),
+    "pi0_decode_attention_split": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
+                                             C.c_int, C.c_int, c_ptr]),
     "pi0_position_ids": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr]),
     "pi0_adapter_resize_normalize": (C.c_int, [c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr,
                                                C.c_int, c_ptr, c_ptr, C.c_int, C.c_float, C.c_float, C.c_float, c_ptr]),

@@ -66,6 +66,19 @@ int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache,
   return decode_attention(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch, num_sms, (cudaStream_t)stream);
 }
 
+int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                               const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, void* stream) {
+  return decode_attention_batch(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch, (cudaStream_t)stream);
+}
+
+int pi0_decode_attention_split(const void* q, const void* kcache, const void* vtcache, void* att, void* scratch,
+                               const uint8_t* pad, const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch,
+                               void* stream) {
+  return decode_attention_split(q, kcache, vtcache, att, scratch, pad, cum, B, S, P, kv_pitch, vt_pitch,
+                                (cudaStream_t)stream);
+}
+
+
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream) {
   return position_ids(pad, B, P, S, prefix_pos, suffix_pos, (cudaStream_t)stream);
 }

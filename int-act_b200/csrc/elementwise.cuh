@@ -24,6 +24,17 @@ int cast_f32(const float* in, T* out, int64_t n, cudaStream_t s);
 int decode_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
                      const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);
 
+// the same attention as two wide launches (attn_split.cu); scratch = bf16 [B*8*S, roundup(P+S, 32)]
+bool decode_attention_split_supported(int S, int P);
+int decode_attention_split(const void* q, const void* kcache, const void* vtcache, void* att, void* scratch,
+                           const uint8_t* pad, const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch,
+                           cudaStream_t s);
+
+// one CTA per sample with K / V^T staged in shared memory (attn_batch.cu): the rollout-batch path
+bool decode_attention_batch_supported(int S, int P);
+int decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                           const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, cudaStream_t s);
+
 // weight-streaming mma.sync GEMMs for M <= 16 suffix rows (gemm_skinny.cu), bf16 only
 bool skinny_supported(int M);
 int skinny_qkv_rope(const void* x, int64_t ldx, const float* gain, const void* wqkv, int M, int K, void* q,

@@ -64,6 +64,7 @@ struct pi0_ctx {
   unsigned* mega_sync;
   void* mega_sc;
   int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
+  bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   Buf bufs[40];
   int nbufs;
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
@@ -149,7 +150,7 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.ye = cv.take("suffix.y", Me * kExpHidden * es);
   x.he = cv.take("suffix.h", Me * kExpHidden * es);
   x.qe = cv.take("suffix.q", Me * kHidden * es);
-  x.sc_e = cv.take("suffix.scores", B * S * kHeads * scp * es);
+  x.sc_e = cv.take("suffix.scores", B * S * kHeads * round_up(kvp, 32) * es);
   x.att_e = cv.take("suffix.att", Me * kHidden * es);
   x.act_e = cv.take("suffix.act", Me * kExpInter * es);
   x.xt_act = cv.take("suffix.xt", B * H * 32 * es);
@@ -288,8 +289,16 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
   if (suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && c->S <= 48 && c->P + c->S <= 640) {
     // denoise step, bf16: scores + masked softmax + P.V in one launch over the cached prefix
     PROF("denoise.attention");
-    PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
-                             c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+    // rollout batches: two wide launches up to B = 12 (latency-bound regime), one CTA pair per sample with K / V^T staged
+    // in shared memory above (bandwidth-bound regime); the one-CTA-per-(sample, head group) kernel otherwise
+    if (B > 12 && c->attn_split && decode_attention_batch_supported(c->S, c->P))
+      PI0_TRY(decode_attention_batch(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch, s));
+    else if (B >= 4 && c->attn_split && decode_attention_split_supported(c->S, c->P))
+      PI0_TRY(decode_attention_split(q, kc, vt, att, c->sc_e, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch,
+                                     c->vt_pitch, s));
+    else
+      PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
+                               c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
   } else {
   // scores[b, t*8+h, j] = rnd(rnd(q . k) * 256^-0.5)   (MQA: the 8 heads of a token are 8 rows against one K)
   {
@@ -377,6 +386,10 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   carve(cv, c, *cfg);
   // persistent denoise kernel: deal the work units to one CTA per SM (bf16 product path only)
   c->mega_ctas = 0;
+  {
+    const char* e = getenv("PI0_ATTN_SPLIT");
+    c->attn_split = !(e && strcmp(e, "0") == 0);
+  }
   const char* mega_env = getenv("PI0_MEGA");
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
   if (cfg->dtype == 0 && cfg->gemm_impl == 0 && !(mega_env && strcmp(mega_env, "0") == 0) && sms >= 64 && sms <= 1024) {

@@ -76,6 +76,17 @@ def test_cuda_graph_replay_matches_eager_launches(cuda):
     assert e1.launches_per_infer[3] > 50
 
 
+def test_rollout_batch_split_attention_parity(cuda):
+    """Batch >= 4: the denoise attention runs as the two wide launches of attn_split.cu (ragged text lengths so the
+    pad mask matters), tcgen05 GEMMs for the suffix rows."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=1024)
+    eng, out, ref, _, _ = _run(cuda, dims, "bf16", B=6, n_valid_text=[72, 9, 33, 2, 50, 17])
+    assert (out - ref).abs().max().item() <= TOL["bf16"]
+    # B > 12: one CTA pair per sample with K / V^T staged in shared memory (attn_batch.cu)
+    eng, out, ref, _, _ = _run(cuda, dims, "bf16", B=14, n_valid_text=[72, 9, 33, 2, 50, 17, 64])
+    assert (out - ref).abs().max().item() <= TOL["bf16"]
+
+
 def test_two_cameras_long_horizon(cuda):
     """LIBERO-shaped (BASELINE config 5): 2 cameras, horizon 16 -> P = 584, S = 17."""
     dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=1024)

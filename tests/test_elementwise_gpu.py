@@ -155,3 +155,23 @@ def test_decode_attention_fused(cuda, B, S, P):
     ref = torch.einsum("bshj,bjd->bshd", pr, v.float()).bfloat16().float().reshape(B * S, 8 * 256)
     err = (att.float().cpu() - ref).abs().max().item()
     assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
+    if S <= 6 and n_keys <= 384:
+        # the two-launch split form (rollout batches) must agree with the fused kernel (same arithmetic, same order
+        # inside every dot product up to the mma k-grouping)
+        att2 = torch.zeros_like(att)
+        scratch = torch.zeros((B * 8 * S, (n_keys + 31) // 32 * 32), dtype=torch.bfloat16, device=cuda)
+        pb.check(pb.lib().pi0_decode_attention_split(pb.ptr(dq), pb.ptr(dk), pb.ptr(dvt), pb.ptr(att2), pb.ptr(scratch),
+                                                     pb.ptr(dpad), pb.ptr(dcum), B, S, P, kv_pitch, vt_pitch, _stream()),
+                 "pi0_decode_attention_split")
+        torch.cuda.synchronize()
+        err2 = (att2.float().cpu() - ref).abs().max().item()
+        assert err2 <= 2 ** -6 * max(1.0, ref.abs().max().item()), err2
+    if S <= 6 and n_keys <= 352:
+        # one CTA per sample, K / V^T staged in shared memory (the rollout-batch path)
+        att3 = torch.zeros_like(att)
+        pb.check(pb.lib().pi0_decode_attention_batch(pb.ptr(dq), pb.ptr(dk), pb.ptr(dvt), pb.ptr(att3), pb.ptr(dpad),
+                                                     pb.ptr(dcum), B, S, P, kv_pitch, vt_pitch, _stream()),
+                 "pi0_decode_attention_batch")
+        torch.cuda.synchronize()
+        err3 = (att3.float().cpu() - ref).abs().max().item()
+        assert err3 <= 2 ** -6 * max(1.0, ref.abs().max().item()), err3

@@ -25,4 +25,25 @@ for B in (1, 8, 64):
         i[0] += 1
         pb.check(pb.lib().pi0_decode_attention(pb.ptr(q), pb.ptr(k[l]), pb.ptr(vt[l]), pb.ptr(att), pb.ptr(pad),
                                                pb.ptr(cum), B, S, P, n, vtp, 148, pb.current_stream()))
-    print(f"B={B}: {graph_time(fn):.2f} us per launch (rotating over {L} layers of KV)")
+    scratch = torch.zeros((B * 8 * S, (n + 31) // 32 * 32), device=dev).bfloat16()
+
+    def fn2():
+        l = i[0] % L
+        i[0] += 1
+        pb.check(pb.lib().pi0_decode_attention_split(pb.ptr(q), pb.ptr(k[l]), pb.ptr(vt[l]), pb.ptr(att), pb.ptr(scratch),
+                                                     pb.ptr(pad), pb.ptr(cum), B, S, P, n, vtp, pb.current_stream()))
+
+    def fn3():
+        l = i[0] % L
+        i[0] += 1
+        pb.check(pb.lib().pi0_decode_attention_batch(pb.ptr(q), pb.ptr(k[l]), pb.ptr(vt[l]), pb.ptr(att), pb.ptr(pad),
+                                                     pb.ptr(cum), B, S, P, n, vtp, pb.current_stream()))
+    print(f"B={B}: batch (smem-staged) {graph_time(fn3):.2f} us")
+    if hasattr(pb.lib(), "pi0_debug_battn_timeline"):
+        import ctypes as C
+        buf = (C.c_ulonglong * 16)()
+        pb.lib().pi0_debug_battn_timeline.argtypes = [C.c_void_p]
+        pb.lib().pi0_debug_battn_timeline(buf)
+        names = ["entry", "pdl wait", "K/Q issued", "K/Q landed", "scores", "softmax", "V landed", "PV+store"]
+        print("   timeline: " + " | ".join(f"{names[i]} +{(buf[i] - buf[0]) / 1e3:.2f}" for i in range(1, 8)) + f" || V issued +{(buf[8]-buf[0])/1e3:.2f} masks ready +{(buf[9]-buf[0])/1e3:.2f}")
+    print(f"B={B}: fused {graph_time(fn):.2f} us, split {graph_time(fn2):.2f} us per attention (rotating over {L} layers of KV)")
