@@ -64,6 +64,7 @@ struct pi0_ctx {
   unsigned* mega_sync;
   void* mega_sc;
   int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
+  bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   Buf bufs[40];
   int nbufs;
@@ -389,6 +390,8 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   {
     const char* e = getenv("PI0_ATTN_SPLIT");
     c->attn_split = !(e && strcmp(e, "0") == 0);
+    const char* f = getenv("PI0_SIGLIP_FUSED");
+    c->siglip_fused = !(f && strcmp(f, "0") == 0);
   }
   const char* mega_env = getenv("PI0_MEGA");
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
@@ -497,6 +500,11 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
       g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
       PI0_TRY(run_gemm(c, "siglip.qkv", g, s));
     }
+    if (c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && c->siglip_fused) {
+      // scores + softmax + P.V of all heads in one launch (attn_siglip.cu)
+      PROF("siglip.attention");
+      PI0_TRY(siglip_attention(c->qk_s, c->vt_s, c->att_s, B, s));
+    } else {
     {  // scores[b,h] = rnd(rnd(q k^T) * 72^-0.5), bidirectional
       GemmProblem g = gemm_problem(c->qk_s, qk_ld, at(c->qk_s, kVisHidden, es), qk_ld, kPatches, kPatches, kVisHd);
       g.nz0 = kVisHeads; g.nz1 = B;
@@ -518,6 +526,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
       g.epi.out = c->att_s; g.epi.ldc = kVisHidden; g.epi.out_z0 = kVisHd;
       g.epi.out_z1 = (int64_t)kPatches * kVisHidden;
       PI0_TRY(run_gemm(c, "siglip.pv", g, s));
+    }
     }
     {  // out_proj + residual (in place on the residual stream: each element is read then written by one thread)
       GemmProblem g = gemm_problem(c->att_s, kVisHidden, lw.wo, kVisHidden, M, kVisHidden, kVisHidden);

@@ -175,3 +175,26 @@ def test_decode_attention_fused(cuda, B, S, P):
         torch.cuda.synchronize()
         err3 = (att3.float().cpu() - ref).abs().max().item()
         assert err3 <= 2 ** -6 * max(1.0, ref.abs().max().item()), err3
+
+
+@pytest.mark.parametrize("B", [1, 3])
+def test_siglip_attention_fused(cuda, B):
+    """Fused SigLIP attention (attn_siglip.cu) against a torch restatement with the reference's rounding points:
+    bf16 scores scaled by 72^-0.5, fp32 softmax, bf16 probabilities, bf16 output."""
+    g = torch.Generator().manual_seed(9)
+    T, H, D = 256, 16, 72
+    qk = (torch.randn((B * T, 2 * H * D), generator=g) * 1.5).bfloat16()
+    v = torch.randn((B, H, T, D), generator=g).bfloat16()
+    vt = v.transpose(2, 3).contiguous()                      # [B, 16, 72, 256]
+    att = torch.zeros((B * T, H * D), dtype=torch.bfloat16, device=cuda)
+    dqk, dvt = qk.to(cuda), vt.to(cuda)
+    pb.check(pb.lib().pi0_siglip_attention(pb.ptr(dqk), pb.ptr(dvt), pb.ptr(att), B, _stream()), "pi0_siglip_attention")
+    torch.cuda.synchronize()
+    q = qk[:, : H * D].float().view(B, T, H, D).transpose(1, 2)
+    k = qk[:, H * D:].float().view(B, T, H, D).transpose(1, 2)
+    sc = (q @ k.transpose(2, 3)).bfloat16().float()
+    sc = (sc * torch.tensor(72 ** -0.5, dtype=torch.float32)).bfloat16().float()
+    pr = torch.softmax(sc, dim=-1).bfloat16().float()
+    ref = (pr @ v.float()).bfloat16().float().transpose(1, 2).reshape(B * T, H * D)
+    err = (att.float().cpu() - ref).abs().max().item()
+    assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
