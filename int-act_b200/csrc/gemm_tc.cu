@@ -625,7 +625,9 @@ void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* 
         const long waves = (tiles + cap - 1) / cap;
         const int chunks = bn / 32;
         const double red_bytes = (double)rows * 32 * 4 * sp * ((chunks + sp - 1) / sp);
-        cost = 1.7 + (double)waves * (2.5 + per * t_kb_skinny[ci] + t_epi / sp + 0.5 + red_bytes / 21000.0);
+        // several waves of clusters keep every SM's tensor pipe busy: MMA / power bound like the persistent kernel
+        cost = 1.7 + (double)waves * (2.5 + per * (waves > 1 ? t_kb[ci] : t_kb_skinny[ci]) + t_epi / sp + 0.5 +
+                                      red_bytes / 21000.0);
       }
       cost += 1e-3 * sp;
       if (cost < best_cost) { best_cost = cost; best_bn = bn; best_s = sp; }

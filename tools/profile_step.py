@@ -23,6 +23,9 @@ st["lang_masks"].fill_(1)
 st["state"][:, :7].normal_(0, 0.5, generator=g)
 for _ in range(passes):
     st["x_t"].normal_(generator=g)
+    eng.lib.pi0_launch_count(1)
     eng._run_static(B)
+    n_launch = int(eng.lib.pi0_launch_count(1))
 torch.cuda.synchronize()
 print("ok", float(st["x_t"].abs().max()))
+print("launches_per_pass", n_launch)
