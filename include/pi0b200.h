@@ -192,10 +192,11 @@ int pi0_decode_attention_split(const void* q, const void* kcache, const void* vt
  * the rollout-batch path (B >= 4). S <= 6, P+S <= 352. */
 int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
                                const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, void* stream);
-/* Fused SigLIP self-attention of one encoder layer (bf16): qk [B*256, 2304] (q | k per token, 16 heads x 72), V^T
- * [B, 16, 72, 256] -> att [B*256, 1152]; scores = rnd(rnd(q.k) * 72^-0.5), fp32 softmax, bf16 probabilities.
+/* Fused SigLIP self-attention of one encoder layer (bf16): qkv [B*256, 3456] (q | k | v per token, 16 heads x 72 each,
+ * exactly what the fused q|k|v Linear writes) -> att [B*256, 1152]; scores = rnd(rnd(q.k) * 72^-0.5), fp32 softmax, bf16
+ * probabilities.
  * Replaces HF SiglipAttention's matmul / softmax / matmul ([mirror] src/model/mvla/mllm.py:182-187). */
-int pi0_siglip_attention(const void* qk, const void* vt, void* att, int B, void* stream);
+int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
 

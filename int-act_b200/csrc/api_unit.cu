@@ -66,8 +66,8 @@ int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache,
   return decode_attention(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch, num_sms, (cudaStream_t)stream);
 }
 
-int pi0_siglip_attention(const void* qk, const void* vt, void* att, int B, void* stream) {
-  return siglip_attention(qk, vt, att, B, (cudaStream_t)stream);
+int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream) {
+  return siglip_attention(qkv, att, B, (cudaStream_t)stream);
 }
 
 int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,

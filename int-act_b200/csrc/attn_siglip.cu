@@ -3,8 +3,9 @@
 // layer at batch 64). Reference: HF SiglipAttention as called by get_image_features ([mirror]
 // /root/reference/src/model/mvla/mllm.py:182-187): scale 72^-0.5, no mask.
 //
-// One CTA = (128 query rows, head, image); 8 warps x 16 rows. K (256 x 72), the CTA's Q rows and V^T (72 x 256) are staged
-// in shared memory with cp.async; the 16 x 256 score tile of a warp lives in registers (mma.sync m16n8k16, k padded
+// One CTA = (128 query rows, head, image); 8 warps x 16 rows. K, V (256 x 72 each, row-major exactly as the fused q|k|v
+// GEMM wrote them - no transposed copy of V exists any more) and the CTA's Q rows are staged in shared memory with
+// cp.async; the B fragments of P.V come out of the row-major V tile through ldmatrix.trans; the 16 x 256 score tile of a warp lives in registers (mma.sync m16n8k16, k padded
 // 72 -> 80 with zeros), the softmax runs on the accumulator fragments (row statistics over the 4 lanes of a quad), and the
 // bf16 probabilities are re-used directly as the A fragments of P.V (accumulator layout = A-operand layout).
 // Rounding points of the reference under autocast(bf16): scores = rnd(rnd(q.k) * 72^-0.5), softmax in fp32,
@@ -20,9 +21,9 @@ constexpr int kHdS = 72;         // head dim
 constexpr int kHeadsS = 16;
 constexpr int kHid = kHeadsS * kHdS;   // 1152
 constexpr int kQKPitch = 88;     // bf16 elements per staged Q / K row (176 B: conflict-free 4-byte fragment loads)
-constexpr int kVPitch = 264;     // bf16 elements per staged V^T row (528 B)
 constexpr int kQRows = 128;      // query rows per CTA
-constexpr size_t kSmemBytes = (size_t)(kT + kQRows) * kQKPitch * 2 + (size_t)kHdS * kVPitch * 2;
+constexpr int kLd = 3 * kHid;    // row pitch of the fused q|k|v activation (3456)
+constexpr size_t kSmemBytes = (size_t)(2 * kT + kQRows) * kQKPitch * 2;
 
 __device__ __forceinline__ void cp16(void* dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
@@ -33,38 +34,38 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// qk  [B*256, 2304]: q(b, t, h, d) at (b*256 + t) * 2304 + h*72 + d, k at + 1152
-// vt  [B, 16, 72, 256]: V^T
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& r0, uint32_t& r1, const void* p) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(smem_u32(p)));
+}
+
+// qkv [B*256, 3456]: q(b, t, h, d) at (b*256 + t) * 3456 + h*72 + d, k at + 1152, v at + 2304
 // att [B*256, 1152]
-__global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restrict__ qk, const bf16* __restrict__ vt,
-                                                             bf16* __restrict__ att, float scale) {
+__global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restrict__ qk, bf16* __restrict__ att,
+                                                             float scale) {
   pdl_trigger();
   extern __shared__ __align__(16) uint8_t smem_raw[];
   bf16* Ks = reinterpret_cast<bf16*>(smem_raw);            // [256][88]
-  bf16* Qs = Ks + kT * kQKPitch;                           // [128][88]
-  bf16* Vs = Qs + kQRows * kQKPitch;                       // [72][264]
+  bf16* Vs = Ks + kT * kQKPitch;                           // [256][88] row-major V
+  bf16* Qs = Vs + kT * kQKPitch;                           // [128][88]
   const int qblk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t4 = lane & 3;
   pdl_wait();
 
-  // ---- stage K, Q (9 chunks of 16 B per row; dims 72..87 zero) and V^T -----------------------------------------------
-  const bf16* kbase = qk + (int64_t)b * kT * (2 * kHid) + kHid + h * kHdS;
-  const bf16* qbase = qk + ((int64_t)b * kT + qblk * kQRows) * (2 * kHid) + h * kHdS;
-  for (int i = threadIdx.x; i < (kT + kQRows) * 11; i += 256) {
+  // ---- stage K, V, Q (9 chunks of 16 B per row; dims 72..87 zero) -----------------------------------------------------
+  const bf16* kbase = qk + (int64_t)b * kT * kLd + kHid + h * kHdS;            // V rows are kHid further
+  const bf16* qbase = qk + ((int64_t)b * kT + qblk * kQRows) * kLd + h * kHdS;
+  for (int i = threadIdx.x; i < (2 * kT + kQRows) * 11; i += 256) {
     const int row = i / 11, ci = i - row * 11;
-    bf16* dst = (row < kT ? Ks + row * kQKPitch : Qs + (row - kT) * kQKPitch) + ci * 8;
+    bf16* dst = Ks + row * kQKPitch + ci * 8;               // Ks | Vs | Qs are contiguous
     if (ci < 9) {
-      const bf16* src = (row < kT ? kbase + (int64_t)row * (2 * kHid) : qbase + (int64_t)(row - kT) * (2 * kHid)) + ci * 8;
-      cp16(dst, src);
+      const bf16* src = row < kT ? kbase + (int64_t)row * kLd
+                                 : row < 2 * kT ? kbase + kHid + (int64_t)(row - kT) * kLd
+                                                : qbase + (int64_t)(row - 2 * kT) * kLd;
+      cp16(dst, src + ci * 8);
     } else {
       *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
     }
-  }
-  const bf16* vbase = vt + ((int64_t)b * kHeadsS + h) * kHdS * kT;
-  for (int i = threadIdx.x; i < kHdS * 32; i += 256) {
-    const int row = i >> 5, ci = i & 31;
-    cp16(Vs + row * kVPitch + ci * 8, vbase + (int64_t)row * kT + ci * 8);
   }
   asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -139,10 +140,13 @@ __global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restr
     for (int e = 0; e < 4; ++e) o[dt][e] = 0.0f;
 #pragma unroll
   for (int kk = 0; kk < 16; ++kk) {
+    // lanes 0-15 address the 16 key rows of this k-step; ldmatrix.trans hands every lane (keys 2 t4, 2 t4 + 1; dim g)
+    const bf16* vrow = Vs + (kk * 16 + (lane & 15)) * kQKPitch;
 #pragma unroll
     for (int dt = 0; dt < 9; ++dt) {
-      const bf16* vr = Vs + (dt * 8 + g) * kVPitch + kk * 16 + 2 * t4;
-      mma_bf16_16816(o[dt], pa[kk][0], pa[kk][1], pa[kk][2], pa[kk][3], lds32(vr), lds32(vr + 8));
+      uint32_t b0, b1;
+      ldmatrix_x2_trans(b0, b1, vrow + dt * 8);
+      mma_bf16_16816(o[dt], pa[kk][0], pa[kk][1], pa[kk][2], pa[kk][3], b0, b1);
     }
   }
   bf16* out0 = att + ((int64_t)b * kT + qblk * kQRows + r0 + g) * kHid + h * kHdS + 2 * t4;
@@ -156,15 +160,15 @@ __global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restr
 
 }  // namespace
 
-int siglip_attention(const void* qk, const void* vt, void* att, int B, cudaStream_t s) {
-  PI0_REQUIRE(qk && vt && att && B >= 1, "siglip_attention: bad argument");
+int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s) {
+  PI0_REQUIRE(qkv && att && B >= 1, "siglip_attention: bad argument");
   static bool attr_set = false;
   if (!attr_set) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(siglip_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     attr_set = true;
   }
   PI0_CHECK_CUDA(launch_pdl(siglip_attn_kernel, dim3(kT / kQRows, kHeadsS, B), dim3(256), kSmemBytes, s, 1,
-                            (const bf16*)qk, (const bf16*)vt, (bf16*)att, 0.11785113019775793f));
+                            (const bf16*)qkv, (bf16*)att, 0.11785113019775793f));
   ++g_launch_count;
   return 0;
 }

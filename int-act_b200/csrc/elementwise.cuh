@@ -35,8 +35,8 @@ bool decode_attention_batch_supported(int S, int P);
 int decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
                            const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, cudaStream_t s);
 
-// fused SigLIP self-attention (attn_siglip.cu), bf16 only: qk [B*256, 2304], V^T [B,16,72,256] -> att [B*256, 1152]
-int siglip_attention(const void* qk, const void* vt, void* att, int B, cudaStream_t s);
+// fused SigLIP self-attention (attn_siglip.cu), bf16 only: fused q|k|v [B*256, 3456] -> att [B*256, 1152]
+int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s);
 
 // weight-streaming mma.sync GEMMs for M <= 16 suffix rows (gemm_skinny.cu), bf16 only
 bool skinny_supported(int M);

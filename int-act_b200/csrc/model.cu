@@ -133,7 +133,7 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.col = cv.take("siglip.col", Ms * kPatchK * es);
   x.xs = cv.take("siglip.x", Ms * kVisHidden * es);
   x.hs = cv.take("siglip.h", Ms * kVisHidden * es);
-  x.qk_s = cv.take("siglip.qk", Ms * 2 * kVisHidden * es);
+  x.qk_s = cv.take("siglip.qk", Ms * 3 * kVisHidden * es);  // q|k (+v on the fused-attention path)
   x.vt_s = cv.take("siglip.vt", B * kVisHeads * kVisHd * kPatches * es);
   x.sc_s = cv.take("siglip.scores", B * kVisHeads * kPatches * kPatches * es);
   x.att_s = cv.take("siglip.att", Ms * kVisHidden * es);
@@ -492,18 +492,25 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
   for (int l = 0; l < c->cfg.n_siglip_layers; ++l) {
     const pi0_siglip_layer_w& lw = w.sig[l];
     PI0_TRY(run_layernorm(c, "siglip.layernorm", c->xs, c->hs, lw.ln1_w, lw.ln1_b, M, kVisHidden, s));
-    {  // fused q|k|v projection; the V columns are written transposed per head for the P.V GEMM
+    const bool fused_attn = c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && c->siglip_fused;
+    {  // fused q|k|v projection. Fused-attention path: plain [M, 3456] output. Per-op path: the V columns are written
+       // transposed per head for the P.V GEMM
       GemmProblem g = gemm_problem(c->hs, kVisHidden, lw.wqkv, kVisHidden, M, 3 * kVisHidden, kVisHidden);
       g.bn = 0;
-      g.epi.out = c->qk_s; g.epi.ldc = qk_ld; g.epi.bias = lw.bqkv;
-      g.epi.vt = c->vt_s; g.epi.vt_col0 = 2 * kVisHidden; g.epi.vt_hd = kVisHd; g.epi.vt_heads = kVisHeads;
-      g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
+      g.epi.out = c->qk_s; g.epi.bias = lw.bqkv;
+      if (fused_attn) {
+        g.epi.ldc = 3 * kVisHidden;
+      } else {
+        g.epi.ldc = qk_ld;
+        g.epi.vt = c->vt_s; g.epi.vt_col0 = 2 * kVisHidden; g.epi.vt_hd = kVisHd; g.epi.vt_heads = kVisHeads;
+        g.epi.vt_rpb = kPatches; g.epi.vt_toff = 0; g.epi.vt_pitch = kPatches;
+      }
       PI0_TRY(run_gemm(c, "siglip.qkv", g, s));
     }
-    if (c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && c->siglip_fused) {
+    if (fused_attn) {
       // scores + softmax + P.V of all heads in one launch (attn_siglip.cu)
       PROF("siglip.attention");
-      PI0_TRY(siglip_attention(c->qk_s, c->vt_s, c->att_s, B, s));
+      PI0_TRY(siglip_attention(c->qk_s, c->att_s, B, s));
     } else {
     {  // scores[b,h] = rnd(rnd(q k^T) * 72^-0.5), bidirectional
       GemmProblem g = gemm_problem(c->qk_s, qk_ld, at(c->qk_s, kVisHidden, es), qk_ld, kPatches, kPatches, kVisHd);

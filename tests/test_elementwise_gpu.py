@@ -185,10 +185,10 @@ def test_siglip_attention_fused(cuda, B):
     T, H, D = 256, 16, 72
     qk = (torch.randn((B * T, 2 * H * D), generator=g) * 1.5).bfloat16()
     v = torch.randn((B, H, T, D), generator=g).bfloat16()
-    vt = v.transpose(2, 3).contiguous()                      # [B, 16, 72, 256]
+    qkv = torch.cat([qk, v.transpose(1, 2).reshape(B * T, H * D)], dim=1).contiguous()     # [B*256, 3456]
     att = torch.zeros((B * T, H * D), dtype=torch.bfloat16, device=cuda)
-    dqk, dvt = qk.to(cuda), vt.to(cuda)
-    pb.check(pb.lib().pi0_siglip_attention(pb.ptr(dqk), pb.ptr(dvt), pb.ptr(att), B, _stream()), "pi0_siglip_attention")
+    dqkv = qkv.to(cuda)
+    pb.check(pb.lib().pi0_siglip_attention(pb.ptr(dqkv), pb.ptr(att), B, _stream()), "pi0_siglip_attention")
     torch.cuda.synchronize()
     q = qk[:, : H * D].float().view(B, T, H, D).transpose(1, 2)
     k = qk[:, H * D:].float().view(B, T, H, D).transpose(1, 2)
