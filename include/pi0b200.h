@@ -210,6 +210,13 @@ int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_po
 int pi0_adapter_resize_normalize(const uint8_t* images, float* out, int B, int H, int W, int out_h, int out_w,
                                  const int32_t* x_idx, const int16_t* x_w, int x_prec, const int32_t* y_idx,
                                  const int16_t* y_w, int y_prec, float rescale, float mean, float stdv, void* stream);
+/* The single-observation adapter's resize: cv2.resize(img, size, interpolation=cv2.INTER_LANCZOS4) on uint8
+ * (/root/reference/src/experiments/env_adapters/simpler.py:47-51) + the same normalisation. 8-tap separable Lanczos,
+ * 11-bit fixed-point coefficients; the caller passes per-axis tables ofs i32 [out] (floor of the source coordinate) and
+ * coef i16 [out,8]. Bit-exact with OpenCV's generic 8U path. */
+int pi0_adapter_lanczos4_normalize(const uint8_t* images, float* out, int B, int H, int W, int out_h, int out_w,
+                                   const int32_t* x_ofs, const int16_t* x_coef, const int32_t* y_ofs,
+                                   const int16_t* y_coef, float rescale, float mean, float stdv, void* stream);
 /* eef [B,8] (f32 or f64: pos | quat wxyz | gripper) -> state f32 [B,7]: quat -> R -> R.default_rot^T -> euler sxyz, then
  * norm_type 0: bound with (p01, p99), clipped to [-1,1]; 1: gaussian with (mean, std). round_bf16 rounds f64 -> bf16
  * like torch.as_tensor(proprio, dtype=bfloat16) (simplerMS3.py:66-88,153-165). */

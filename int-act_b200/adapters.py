@@ -8,8 +8,9 @@ uploaded ONCE as raw uint8 frames + eef poses, and resize / normalisation / quat
 (csrc/adapters.cu, C ABI `pi0_adapter_*`) instead of a per-sample Python loop on the host.
 
 There is no CPU fallback for the batch adapter: without the library / a CUDA device construction fails.
-The single-observation adapter keeps the reference's host-side `cv2.resize(..., INTER_LANCZOS4)` (same library call,
-hence identical pixels); its proprio / post-processing use the same kernels with B = 1.
+The single-observation adapter resizes with a CUDA restatement of OpenCV's uint8 INTER_LANCZOS4 (8-tap separable,
+11-bit fixed-point coefficients; bit-exact against cv2 itself in the tests); its proprio / post-processing use the same
+kernels with B = 1. Neither adapter needs OpenCV at run time.
 """
 from __future__ import annotations
 
@@ -47,6 +48,37 @@ def u8_bilinear_tables(in_size: int, out_size: int):
             break
     wi = np.where(w * (1 << prec) < 0, w * (1 << prec) - 0.5, w * (1 << prec) + 0.5).astype(np.int64).astype(np.int16)
     return idx, wi, prec
+
+
+def lanczos4_tables(in_size: int, out_size: int):
+    """Per-axis tables of OpenCV's INTER_LANCZOS4 resize on uint8 (the call of simpler.py:47-51; imgproc resize.cpp):
+    source offset = floor(fx) with fx = float32((d + 0.5) * scale - 0.5), 8 float32 coefficients from
+    interpolateLanczos4 (sin / cos of -(x + 3 - i) pi / 4 over y^2, normalised), converted to 11-bit fixed point with
+    saturate_cast<short> (round half to even). ofs int32 [out], coef int16 [out, 8]."""
+    s45 = 0.70710678118654752440084436210485
+    cs = ((1, 0), (-s45, -s45), (0, 1), (s45, -s45), (-1, 0), (s45, s45), (0, -1), (-s45, s45))
+    scale = float(in_size) / out_size
+    ofs = np.zeros(out_size, np.int32)
+    coef = np.zeros((out_size, 8), np.int16)
+    for d in range(out_size):
+        f = np.float32((d + 0.5) * scale - 0.5)
+        sx = int(math.floor(f))
+        x = np.float32(f - np.float32(sx))
+        c = np.zeros(8, np.float32)
+        if x < np.finfo(np.float32).eps:
+            c[3] = 1.0
+        else:
+            y0 = -(float(x) + 3) * math.pi * 0.25
+            s0, c0 = math.sin(y0), math.cos(y0)
+            total = np.float32(0)
+            for i in range(8):
+                y = -(float(x) + 3 - i) * math.pi * 0.25
+                c[i] = np.float32((cs[i][0] * s0 + cs[i][1] * c0) / (y * y))
+                total = np.float32(total + c[i])
+            c = (c * (np.float32(1.0) / total)).astype(np.float32)
+        ofs[d] = sx
+        coef[d] = np.clip(np.rint(c * np.float32(2048)), -32768, 32767).astype(np.int16)
+    return ofs, coef
 
 
 def _cfg_get(config, path: Sequence[str], default=None):
@@ -115,6 +147,26 @@ class _GpuAdapterBase:
                                                        pb.current_stream()), "pi0_adapter_resize_normalize")
         return out
 
+    def lanczos4_normalize(self, images_u8: torch.Tensor) -> torch.Tensor:
+        """uint8 [B, H, W, 3] on the device -> float32 [B, 3, h, w] in [-1, 1]: cv2.INTER_LANCZOS4 resize (bit-exact with
+        OpenCV's generic uint8 path) + x/255 + (x-0.5)/0.5 (simpler.py:47-65)."""
+        B, H, W, C = images_u8.shape
+        if C != 3 or images_u8.dtype != torch.uint8:
+            raise ValueError(f"expected uint8 [B, H, W, 3] frames, got {images_u8.dtype} {tuple(images_u8.shape)}")
+        ow, oh = self.image_size  # cv2.resize takes dsize = (width, height)
+        key = ("lanczos4", H, W, oh, ow)
+        if key not in self._tables:
+            xo, xc = lanczos4_tables(W, ow)
+            yo, yc = lanczos4_tables(H, oh)
+            self._tables[key] = tuple(torch.from_numpy(t).to(self.device) for t in (xo, xc, yo, yc))
+        xo, xc, yo, yc = self._tables[key]
+        out = torch.empty((B, 3, oh, ow), dtype=torch.float32, device=self.device)
+        images_u8 = images_u8.contiguous()
+        pb.check(self.lib.pi0_adapter_lanczos4_normalize(pb.ptr(images_u8), pb.ptr(out), B, H, W, oh, ow, pb.ptr(xo),
+                                                         pb.ptr(xc), pb.ptr(yo), pb.ptr(yc), 1.0 / 255.0, 0.5, 0.5,
+                                                         pb.current_stream()), "pi0_adapter_lanczos4_normalize")
+        return out
+
     def proprio(self, eef: torch.Tensor) -> torch.Tensor:
         """eef [B, 8] (float32 / float64, device) -> normalised state float32 [B, 7] carrying the rounding of
         `torch.as_tensor(proprio, dtype=self.dtype)` (simplerMS3.py:66-88,153-165)."""
@@ -170,11 +222,13 @@ class BridgeSimplerAdapter(_GpuAdapterBase):
     "observation.state": the simulator's nested obs dict (eef pose under ["agent"]["eef_pos"]), "task": str}."""
 
     def preprocess(self, obs: dict) -> dict:
-        import cv2  # same call as the reference (simpler.py:47-51): identical pixels by construction
-
-        image = cv2.resize(np.asarray(obs["observation.images.top"]), self.image_size, interpolation=cv2.INTER_LANCZOS4)
-        frames = torch.as_tensor(image, dtype=torch.uint8)[None].to(self.device, non_blocking=True)
-        images = self.resize_normalize(frames)  # already image_size: only x/255 and (x-0.5)/0.5 remain
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore", UserWarning)
+            frame = torch.as_tensor(np.asarray(obs["observation.images.top"]))
+        if frame.dtype != torch.uint8:
+            frame = frame.to(torch.uint8)
+        # cv2.resize(..., INTER_LANCZOS4) + process_images as one kernel on the raw frame (simpler.py:47-65)
+        images = self.lanczos4_normalize(frame[None].to(self.device, non_blocking=True))
         eef = np.asarray(obs["observation.state"]["agent"]["eef_pos"])
         state = self.proprio(torch.as_tensor(eef)[None].to(self.device, non_blocking=True))
         return {"observation.images.top": images, "observation.state": state, "task": [obs["task"]]}

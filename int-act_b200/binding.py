@@ -108,6 +108,8 @@ SIGNATURES = {
     "pi0_position_ids": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr]),
     "pi0_adapter_resize_normalize": (C.c_int, [c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr,
                                                C.c_int, c_ptr, c_ptr, C.c_int, C.c_float, C.c_float, C.c_float, c_ptr]),
+    "pi0_adapter_lanczos4_normalize": (C.c_int, [c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr,
+                                                 c_ptr, c_ptr, C.c_float, C.c_float, C.c_float, c_ptr]),
     "pi0_adapter_proprio": (C.c_int, [c_ptr, C.c_int, c_ptr, C.c_int, c_ptr, c_ptr, C.c_int, C.c_int, c_ptr]),
     "pi0_adapter_postprocess": (C.c_int, [c_ptr, c_ptr, C.c_int, c_ptr, c_ptr, C.c_int, c_ptr]),
 }

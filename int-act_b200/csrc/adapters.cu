@@ -51,6 +51,52 @@ __global__ void adapter_resize_norm_kernel(const uint8_t* __restrict__ img, floa
   }
 }
 
+// cv2.resize(..., INTER_LANCZOS4) on uint8 (the call of simpler.py:47-51; OpenCV imgproc resize.cpp, 8-tap separable
+// Lanczos with 11-bit fixed-point coefficients): horizontal pass in int32 over the 8 clamped source rows, vertical pass,
+// then (v + 2^21) >> 22 saturated to uint8. One thread per output pixel, all three channels. Bit-exact integer work.
+__global__ void adapter_lanczos4_norm_kernel(const uint8_t* __restrict__ img, float* __restrict__ out, int B, int H, int W,
+                                             int oh, int ow, const int* __restrict__ xofs, const short* __restrict__ xc,
+                                             const int* __restrict__ yofs, const short* __restrict__ yc, float rescale,
+                                             float mean, float stdv) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t n = (int64_t)B * oh * ow;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % ow), oy = (int)((i / ow) % oh), b = (int)(i / ((int64_t)ow * oh));
+    const uint8_t* base = img + (int64_t)b * H * W * 3;
+    int xi[8], cx[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      xi[k] = min(max(xofs[ox] - 3 + k, 0), W - 1);
+      cx[k] = xc[ox * 8 + k];
+    }
+    long long acc[3] = {0, 0, 0};
+#pragma unroll 1
+    for (int ky = 0; ky < 8; ++ky) {
+      const int y = min(max(yofs[oy] - 3 + ky, 0), H - 1);
+      const uint8_t* row = base + (int64_t)y * W * 3;
+      int h[3] = {0, 0, 0};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint8_t* px = row + xi[k] * 3;
+        h[0] += px[0] * cx[k];
+        h[1] += px[1] * cx[k];
+        h[2] += px[2] * cx[k];
+      }
+      const long long cy = yc[oy * 8 + ky];
+      acc[0] += cy * h[0];
+      acc[1] += cy * h[1];
+      acc[2] += cy * h[2];
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const long long v = (acc[c] + (1ll << 21)) >> 22;
+      const int u = (int)min(max(v, 0ll), 255ll);
+      out[(((int64_t)b * 3 + c) * oh + oy) * ow + ox] = __fdiv_rn(__fsub_rn(__fmul_rn((float)u, rescale), mean), stdv);
+    }
+  }
+}
+
 struct Mat3 { double m[3][3]; };
 
 __device__ __forceinline__ Mat3 quat2mat_d(double w, double x, double y, double z) {
@@ -179,6 +225,20 @@ int pi0_adapter_resize_normalize(const uint8_t* images, float* out, int B, int H
   PI0_CHECK_CUDA(launch_pdl(adapter_resize_norm_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, 1, images, out, B,
                             H, W, out_h, out_w, (const int*)x_idx, (const short*)x_w, x_prec, (const int*)y_idx,
                             (const short*)y_w, y_prec, rescale, mean, stdv));
+  ++g_launch_count;
+  return 0;
+}
+
+int pi0_adapter_lanczos4_normalize(const uint8_t* images, float* out, int B, int H, int W, int out_h, int out_w,
+                                   const int32_t* x_ofs, const int16_t* x_coef, const int32_t* y_ofs,
+                                   const int16_t* y_coef, float rescale, float mean, float stdv, void* stream) {
+  PI0_REQUIRE(images && out && x_ofs && x_coef && y_ofs && y_coef, "pi0_adapter_lanczos4_normalize: null argument");
+  PI0_REQUIRE(B >= 1 && H >= 1 && W >= 1 && out_h >= 1 && out_w >= 1, "pi0_adapter_lanczos4_normalize: bad sizes");
+  const int64_t n = (int64_t)B * out_h * out_w;
+  const int grid = (int)((n + 127) / 128 < 148 * 16 ? (n + 127) / 128 : 148 * 16);
+  PI0_CHECK_CUDA(launch_pdl(adapter_lanczos4_norm_kernel, dim3(grid), dim3(128), 0, (cudaStream_t)stream, 1, images, out,
+                            B, H, W, out_h, out_w, (const int*)x_ofs, (const short*)x_coef, (const int*)y_ofs,
+                            (const short*)y_coef, rescale, mean, stdv));
   ++g_launch_count;
   return 0;
 }

@@ -161,6 +161,13 @@ def main():
         for t in range(4):
             ax, ang = geo.euler2axangle(*rex[b, t, 3:6])
             env[b, t] = np.concatenate([rex[b, t, :3], ax * ang, [2.0 * (acts[b, t, -1] > 0.5) - 1.0]])
+    # single adapter resize: the reference's own call (simpler.py:47-51) on small and full-size frames
+    import cv2
+    lz_small = cv2.resize(imgs[0].numpy(), (28, 28), interpolation=cv2.INTER_LANCZOS4)
+    lz_frame = torch.randint(0, 256, (480, 640, 3), generator=torch.Generator().manual_seed(7), dtype=torch.uint8).numpy()
+    lz_full = cv2.resize(lz_frame, (224, 224), interpolation=cv2.INTER_LANCZOS4)
+    np.savez_compressed(f"{OUT}/adapter_lanczos.npz", small=lz_small, full_checksum=np.array([int(lz_full.astype(np.int64).sum())]),
+                        full_corner=lz_full[:6, :6], full_last=lz_full[-3:, -3:], cv2_version=np.array([cv2.__version__]))
     np.savez_compressed(f"{OUT}/adapter_batch.npz", imgs=imgs.numpy(), resized=res.numpy(), proc=pimgs.numpy(),
                         full_seed=np.array([7]), full_checksum=np.array([int(res_full.long().sum())]),
                         full_corner=res_full[0, :, :4, :4].numpy(), eef=eef, raw=raw, state=state, acts=acts, env=env,

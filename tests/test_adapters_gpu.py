@@ -79,15 +79,36 @@ def test_proprio_and_postprocess_vs_oracle(cuda):
     assert torch.equal(got, torch.as_tensor(d["state"], dtype=torch.bfloat16).float())
 
 
-def test_single_adapter_matches_reference_calls(cuda):
-    cv2 = pytest.importorskip("cv2")
+@pytest.mark.parametrize("hw", [(480, 640), (224, 224), (100, 37), (512, 512)])
+def test_lanczos4_bit_exact_vs_oracle_and_opencv(cuda, hw):
     d = np.load(os.path.join(G, "adapter_batch.npz"))
     a = _adapter("BridgeSimplerAdapter", _stats(d))
-    frame = np.random.default_rng(5).integers(0, 256, (480, 640, 3), dtype=np.uint8)
+    frames = torch.randint(0, 256, (2, hw[0], hw[1], 3), generator=torch.Generator().manual_seed(4), dtype=torch.uint8)
+    got = a.lanczos4_normalize(frames.cuda()).cpu().numpy()
+    ref = ao.process_images(np.stack([ao.resize_u8_lanczos4(f, 224, 224) for f in frames.numpy()]).transpose(0, 3, 1, 2))
+    assert np.array_equal(got, ref)
+    try:
+        import cv2
+    except ImportError:
+        return
+    ref2 = np.stack([cv2.resize(f, (224, 224), interpolation=cv2.INTER_LANCZOS4) for f in frames.numpy()])
+    assert np.array_equal(got, ao.process_images(ref2.transpose(0, 3, 1, 2)))
+
+
+def test_single_adapter_matches_reference_calls(cuda):
+    d = np.load(os.path.join(G, "adapter_batch.npz"))
+    lz = np.load(os.path.join(G, "adapter_lanczos.npz"))
+    a = _adapter("BridgeSimplerAdapter", _stats(d))
+    frame = torch.randint(0, 256, (480, 640, 3), generator=torch.Generator().manual_seed(7), dtype=torch.uint8).numpy()
     eef = d["eef"][0].astype(np.float32)
     out = a.preprocess({"observation.images.top": frame, "observation.state": {"agent": {"eef_pos": eef}}, "task": "t"})
-    ref_img = cv2.resize(frame, (224, 224), interpolation=cv2.INTER_LANCZOS4).transpose(2, 0, 1)[None]
-    assert np.array_equal(out["observation.images.top"].cpu().numpy(), ao.process_images(ref_img))
+    img = out["observation.images.top"].cpu().numpy()
+    # undo the normalisation exactly: (x * (1/255) - 0.5) / 0.5 is injective on 0..255
+    lut = ao.process_images(np.arange(256, dtype=np.uint8).reshape(1, 1, 1, 256))[0, 0, 0]
+    u8 = np.searchsorted(lut, img).astype(np.uint8)
+    assert np.array_equal(lut[u8], img)
+    assert int(u8.astype(np.int64).sum()) == int(lz["full_checksum"][0])           # the frame cv2 resized at fixture time
+    assert np.array_equal(u8[0].transpose(1, 2, 0)[:6, :6], lz["full_corner"])
     assert out["task"] == ["t"] and tuple(out["observation.state"].shape) == (1, 7)
     env = a.postprocess(torch.from_numpy(d["acts"][0]).cuda())
     assert env.shape == (4, 7) and np.abs(env - d["env"][0]).max() <= 1e-12

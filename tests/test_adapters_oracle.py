@@ -43,8 +43,34 @@ def test_batch_adapter_against_reference_vectors():
     assert np.array_equal(r.transpose(2, 0, 1)[:, :4, :4], d["full_corner"])
 
 
+def test_lanczos4_against_opencv_vectors():
+    """The single adapter's resize (simpler.py:47-51): the integer restatement of OpenCV's uint8 INTER_LANCZOS4 against
+    frames resized by cv2 itself when the fixtures were generated (and against the installed cv2, when there is one)."""
+    import torch
+
+    d = np.load(os.path.join(G, "adapter_lanczos.npz"))
+    imgs = np.load(os.path.join(G, "adapter_batch.npz"))["imgs"]
+    assert np.array_equal(ao.resize_u8_lanczos4(imgs[0], 28, 28), d["small"])
+    frame = torch.randint(0, 256, (480, 640, 3), generator=torch.Generator().manual_seed(7), dtype=torch.uint8).numpy()
+    r = ao.resize_u8_lanczos4(frame, 224, 224)
+    assert int(r.astype(np.int64).sum()) == int(d["full_checksum"][0])
+    assert np.array_equal(r[:6, :6], d["full_corner"]) and np.array_equal(r[-3:, -3:], d["full_last"])
+    try:
+        import cv2
+    except ImportError:
+        return
+    rng = np.random.default_rng(2)
+    for (H, W, oh, ow) in ((48, 64, 22, 22), (100, 37, 64, 48), (256, 256, 224, 224)):
+        img = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        assert np.array_equal(ao.resize_u8_lanczos4(img, oh, ow), cv2.resize(img, (ow, oh), interpolation=cv2.INTER_LANCZOS4))
+
+
 def test_product_resize_tables_match_oracle():
-    from int_act_b200.adapters import u8_bilinear_tables
+    from int_act_b200.adapters import lanczos4_tables, u8_bilinear_tables
+
+    for n_in, n_out in ((640, 224), (480, 224), (224, 224), (37, 64)):
+        a, b = lanczos4_tables(n_in, n_out), ao.lanczos4_tables(n_in, n_out)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
 
     for n_in, n_out in ((640, 224), (480, 224), (224, 224), (37, 224), (512, 224), (60, 28)):
         a, b = u8_bilinear_tables(n_in, n_out), ao.u8_bilinear_tables(n_in, n_out)
