@@ -24,6 +24,16 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly ONE JSON line. Libraries write there too (NCCL prints its "NCCL version ..." banner on stdout
+# whatever NCCL_DEBUG_FILE says), so file descriptor 1 is pointed at stderr for the whole process and the JSON line is
+# written to the saved descriptor of the real stdout at the end.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
 
 import torch  # noqa: E402
 
@@ -194,7 +204,7 @@ def reference_arm(args, rank):
         "e2e": {"value": value, "unit": "chunks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # -----------------------------------------------------------------------------------------------------------------
@@ -428,7 +438,7 @@ def b200_arm(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": v, "unit": "chunks/s", "cores": cores, "kind": "port",
                                     "sample": f"fp32 CPU oracle, {len(times)} timed infer_action calls on 1 observation "
                                               f"after 1 warm-up ({sum(times):.1f} s), vocab table cut to 8192 rows"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
