@@ -170,7 +170,8 @@ typedef struct pi0_gemm_desc {
   int32_t splits;    /* split-K factor = thread-block cluster size, 1..8; 0 = pick from the shape */
 } pi0_gemm_desc;
 
-/* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT. */
+/* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT, 2 = tcgen05 single-CTA kernels
+   only, 3 = force the tcgen05 CTA-pair (cta_group::2) kernel. */
 int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream);
 
 int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream);

@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256, 1) batch_attn_kernel(const BatchAttnParam
 #pragma unroll
         for (int i = 0; i < NI; ++i) {
           const int j = i * 32 + lane;
-          if (j < kp) row[j] = __float2bfloat16_rn(v[k][i] * inv);
+          if (j < kp) row[j] = to_bf16(v[k][i] * inv);
         }
       }
     }

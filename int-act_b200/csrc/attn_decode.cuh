@@ -130,7 +130,7 @@ __device__ __forceinline__ void decode_attn_body(uint8_t* smem_raw, const bf16* 
     float* row = sc + r * sc_pitch;
     bf16* prow = reinterpret_cast<bf16*>(row);
     if (r >= R) {  // padding rows of the last m16 tile: zero probabilities
-      for (int j = lane; j < kp; j += 32) prow[j] = __float2bfloat16_rn(0.0f);
+      for (int j = lane; j < kp; j += 32) prow[j] = to_bf16(0.0f);
       continue;
     }
     const int cq = cum[r / hpg];
@@ -160,7 +160,7 @@ __device__ __forceinline__ void decode_attn_body(uint8_t* smem_raw, const bf16* 
 #pragma unroll
     for (int i = 0; i < 20; ++i) {
       const int j = i * 32 + lane;
-      if (j < kp) prow[j] = __float2bfloat16_rn(v[i] * inv);
+      if (j < kp) prow[j] = to_bf16(v[i] * inv);
     }
   }
   attn_sync256();

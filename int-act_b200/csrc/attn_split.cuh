@@ -96,7 +96,7 @@ __device__ __forceinline__ void attn_pv_unit(const PT& p, const bf16* vt, uint8_
     const int r = warp + rr * 8;
     bf16* prow = reinterpret_cast<bf16*>(ptile + r * ppb);
     if (r >= p.S) {
-      for (int j = lane; j < kp; j += 32) prow[j] = __float2bfloat16_rn(0.0f);
+      for (int j = lane; j < kp; j += 32) prow[j] = to_bf16(0.0f);
       continue;
     }
     const int cq = p.cum[r];
@@ -133,7 +133,7 @@ __device__ __forceinline__ void attn_pv_unit(const PT& p, const bf16* vt, uint8_
 #pragma unroll
     for (int i = 0; i < kMegaKeyChunks; ++i) {
       const int j = i * 32 + lane;
-      if (j < kp) prow[j] = __float2bfloat16_rn(v[i] * inv);
+      if (j < kp) prow[j] = to_bf16(v[i] * inv);
     }
   }
   attn_sync256();

@@ -82,14 +82,26 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 // ---------------------------------------------------------------------------------------------
 // numeric helpers
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+// fp32 -> bf16 (round to nearest even). The scalar cvt.rn.bf16.f32 compiles to F2F on the conversion pipe (16 per clock
+// per SM: the tcgen05 GEMM epilogues, which round every accumulator up to three times, were bound by it), whereas the
+// packed cvt.rn.bf16x2.f32 is an F2FP on the ALU path: convert through the packed form with a zero partner. The result
+// of the packed form with the value in the upper half IS the rounded value's fp32 bit pattern.
+__device__ __forceinline__ uint32_t bf16x2_bits(float hi, float lo) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float bf16_round(float x) { return __uint_as_float(bf16x2_bits(x, 0.0f)); }
+__device__ __forceinline__ bf16 to_bf16(float x) {
+  return __ushort_as_bfloat16((unsigned short)(bf16x2_bits(x, 0.0f) >> 16));
+}
 
 // storage-type dependent rounding: activations are bf16 in the product regime, fp32 in check mode
 template <typename T> struct Num;
 template <> struct Num<bf16> {
   static __device__ __forceinline__ float rnd(float x) { return bf16_round(x); }
   static __device__ __forceinline__ float ld(const bf16* p) { return __bfloat162float(*p); }
-  static __device__ __forceinline__ void st(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+  static __device__ __forceinline__ void st(bf16* p, float v) { *p = to_bf16(v); }
   static __device__ __forceinline__ float gelu(float x);
 };
 template <> struct Num<float> {

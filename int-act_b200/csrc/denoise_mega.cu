@@ -351,16 +351,16 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
       const int bb = row / p.S, t = row % p.S;
       if (head < 8) {
         bf16* dst = p.q + (int64_t)row * kQDim + head * 256 + d;
-        dst[0] = __float2bfloat16_rn(o1);
-        dst[128] = __float2bfloat16_rn(o2);
+        dst[0] = to_bf16(o1);
+        dst[128] = to_bf16(o2);
       } else if (head == 8) {
         bf16* dst = kc + ((int64_t)bb * p.kv_pitch + p.P + t) * 256 + d;
-        dst[0] = __float2bfloat16_rn(o1);
-        dst[128] = __float2bfloat16_rn(o2);
+        dst[0] = to_bf16(o1);
+        dst[128] = to_bf16(o2);
       } else {
         bf16* dst = vt + (int64_t)bb * 256 * p.vt_pitch + p.P + t;
-        dst[(int64_t)d * p.vt_pitch] = __float2bfloat16_rn(o1);
-        dst[(int64_t)(d + 128) * p.vt_pitch] = __float2bfloat16_rn(o2);
+        dst[(int64_t)d * p.vt_pitch] = to_bf16(o1);
+        dst[(int64_t)(d + 128) * p.vt_pitch] = to_bf16(o2);
       }
     });
 
@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
       const int n = u * 8 + col;
       const unsigned short xb = __ldcg(reinterpret_cast<const unsigned short*>(x_in) + (int64_t)row * kHidden + n);
       const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(xb));
-      p.y[(int64_t)row * kHidden + n] = __float2bfloat16_rn(v);
+      p.y[(int64_t)row * kHidden + n] = to_bf16(v);
     });
 
     // ---- phase 4: act = gelu_tanh(h . Wg^T) * (h . Wu^T), h = RMSNorm(y) -------------------------------------------
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
     run_units(MEGA_GU, [&](int u, int row, int col, float t0, float t1) {
       const float gt = bf16_round(t0), up = bf16_round(t1);
       const float act = bf16_round(gelu_tanh_fast(gt));
-      p.act[(int64_t)row * kInter + u * 8 + col] = __float2bfloat16_rn(act * up);
+      p.act[(int64_t)row * kInter + u * 8 + col] = to_bf16(act * up);
     });
 
     // ---- phase 5: x = y + act . Wdown^T ----------------------------------------------------------------------------
@@ -416,7 +416,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
       const int n = u * 8 + col;
       const unsigned short yb = __ldcg(reinterpret_cast<const unsigned short*>(p.y) + (int64_t)row * kHidden + n);
       const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(yb));
-      p.x[(int64_t)row * kHidden + n] = __float2bfloat16_rn(v);
+      p.x[(int64_t)row * kHidden + n] = to_bf16(v);
     });
     MEGA_STAMP(14);
   }

@@ -16,6 +16,7 @@ struct GemmProblem {
   int epi_mode;             // EpiMode
   int bn;                   // N tile of the tcgen05 kernel (32/64/128/256; 0 = auto); EPI_ROPE requires 256
   int splits;               // split-K factor = cluster size (1..8; 0 = auto)
+  int pair;                 // CTA-pair (cta_group::2) kernel: 0 = auto, 1 = force, -1 = never
   EpiParams epi;
 };
 
@@ -24,13 +25,14 @@ inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64
   g.A = A; g.lda = lda; g.a_z0 = 0; g.a_z1 = 0;
   g.W = W; g.ldw = ldw; g.w_z0 = 0; g.w_z1 = 0;
   g.M = M; g.N = N; g.K = K; g.nz0 = 1; g.nz1 = 1;
-  g.epi_mode = EPI_STORE; g.bn = 256; g.splits = 0;
+  g.epi_mode = EPI_STORE; g.bn = 256; g.splits = 0; g.pair = 0;
   g.epi = epi_default();
   return g;
 }
 
 // dtype: 0 = bf16 activations/weights (tcgen05 path), 1 = fp32 check mode (SIMT path).
-// impl:  0 = default for the dtype, 1 = force the SIMT kernel (debug cross-check of the tcgen05 path).
+// impl:  0 = default for the dtype, 1 = force the SIMT kernel (debug cross-check of the tcgen05 path),
+//        2 = tcgen05 single-CTA kernels only, 3 = force the tcgen05 CTA-pair kernel.
 int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStream_t stream);
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream);

@@ -149,6 +149,11 @@ template int gemm_simt_launch<bf16>(const GemmProblem&, cudaStream_t);
 int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStream_t stream) {
   if (dtype == 1) return gemm_simt_launch<float>(g, stream);
   if (impl == 1) return gemm_simt_launch<bf16>(g, stream);
+  if (impl == 2 || impl == 3) {
+    GemmProblem f = g;
+    f.pair = impl == 3 ? 1 : -1;
+    return gemm_tc_launch(f, num_sms, stream);
+  }
   return gemm_tc_launch(g, num_sms, stream);
 }
 

@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyParams p) 
         const int n = (c * NT + nt) * 8 + col;
         float v = bf16_round(total(nt, row, col));
         v += __bfloat162float(p.res[(int64_t)row * p.ldr + n]);
-        p.out[(int64_t)row * p.ldc + n] = __float2bfloat16_rn(v);
+        p.out[(int64_t)row * p.ldc + n] = to_bf16(v);
       }
     }
   } else if constexpr (EPI == SK_ROPE) {
@@ -227,16 +227,16 @@ __global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyParams p) 
         const int bb = row / p.S, t = row % p.S;
         if (head < 8) {
           bf16* dst = p.q + (int64_t)row * p.ldq + head * 256 + d;
-          dst[0] = __float2bfloat16_rn(o1);
-          dst[128] = __float2bfloat16_rn(o2);
+          dst[0] = to_bf16(o1);
+          dst[128] = to_bf16(o2);
         } else if (head == 8) {
           bf16* dst = p.kcache + ((int64_t)bb * p.kv_pitch + p.P + t) * 256 + d;
-          dst[0] = __float2bfloat16_rn(o1);
-          dst[128] = __float2bfloat16_rn(o2);
+          dst[0] = to_bf16(o1);
+          dst[128] = to_bf16(o2);
         } else {
           bf16* dst = p.vtcache + (int64_t)bb * 256 * p.vt_pitch + p.P + t;
-          dst[(int64_t)d * p.vt_pitch] = __float2bfloat16_rn(o1);
-          dst[(int64_t)(d + 128) * p.vt_pitch] = __float2bfloat16_rn(o2);
+          dst[(int64_t)d * p.vt_pitch] = to_bf16(o1);
+          dst[(int64_t)(d + 128) * p.vt_pitch] = to_bf16(o2);
         }
       }
     }
@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyParams p) 
         const float gt = bf16_round(total(col >> 3, row, col & 7));
         const float up = bf16_round(total(2 + (col >> 3), row, col & 7));
         const float act = bf16_round(gelu_tanh_fast(gt));
-        p.out[(int64_t)row * p.ldc + c * 16 + col] = __float2bfloat16_rn(act * up);
+        p.out[(int64_t)row * p.ldc + c * 16 + col] = to_bf16(act * up);
       }
     }
   }

@@ -16,8 +16,11 @@ namespace pi0 {
 #ifdef PI0_TIMELINE
 __device__ unsigned long long g_timeline[16];
 #define PI0_STAMP(i) do { if (blockIdx.x == 0) g_timeline[i] = global_timer_ns(); } while (0)
+__device__ unsigned long long g_pair_timeline[2][16][4];  // [rank][tile][mma first issue, last commit, tfull seen, drained]
+#define PAIR_STAMP(r, t, k) do { if (pair == 0 && (t) < 16) g_pair_timeline[r][t][k] = global_timer_ns(); } while (0)
 #else
 #define PI0_STAMP(i) do { } while (0)
+#define PAIR_STAMP(r, t, k) do { } while (0)
 #endif
 
 constexpr int kBM = 128;
@@ -56,6 +59,59 @@ __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, 
   int rr = r - g * span;
   tm = first_m + rr % gsz;
   tn = rr / gsz;
+}
+
+// Epilogue of one 128-row accumulator tile: TMEM lanes of this warp's quadrant -> registers -> fused epilogue -> global.
+// `part` selects which of the NPARTS slices of the tile's column chunks this warp drains (NPARTS warps share a lane
+// quadrant).
+template <int BN, int EPI, int NPARTS = 2>
+__device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& ep, uint32_t taddr, int row, bool row_ok,
+                                           int tn, int z0, int z1, int part) {
+  const int n0 = tn * BN;
+  if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
+    const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
+    constexpr int kTotal = BN / 32;
+    constexpr int kPer = (kTotal + NPARTS - 1) / NPARTS;  // chunks per part
+#pragma unroll 1
+    for (int c = part * kPer; c < min(kTotal, (part + 1) * kPer); ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= sh.N) break;
+      float v[32];
+      tmem_ld_32x32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (row_ok) {
+        if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
+        else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
+      }
+    }
+  } else if constexpr (EPI == EPI_GEGLU) {
+    // tile columns [0, BN/2) are gate rows, [BN/2, BN) the matching up rows (interleaved at pack time)
+    const int n_out = sh.N / 2;
+    constexpr int kTotal = BN / 64;  // (gate, up) chunk pairs
+    constexpr int kPer = (kTotal + NPARTS - 1) / NPARTS;
+#pragma unroll 1
+    for (int c = part * kPer; c < min(kTotal, (part + 1) * kPer); ++c) {
+      const int out_col0 = tn * (BN / 2) + c * 32;
+      if (out_col0 >= n_out) break;
+      float g[32], u[32];
+      tmem_ld_32x32(taddr + c * 32, g);
+      tmem_ld_32x32(taddr + BN / 2 + c * 32, u);
+      tmem_ld_wait();
+      if (row_ok) epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
+    }
+  } else if constexpr (EPI == EPI_ROPE) {
+    static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
+    const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
+    constexpr int kPer = (4 + NPARTS - 1) / NPARTS;
+#pragma unroll 1
+    for (int c = part * kPer; c < min(4, (part + 1) * kPer); ++c) {
+      float x1[32], x2[32];
+      tmem_ld_32x32(taddr + c * 32, x1);
+      tmem_ld_32x32(taddr + 128 + c * 32, x2);
+      tmem_ld_wait();
+      if (row_ok) epi_rope_chunk<bf16>(ep, row, which, tn, c, x1, x2);
+    }
+  }
 }
 
 template <int BN, int EPI>
@@ -211,7 +267,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tile_coords(sh, idx, z, tm, tn);
       const int z0 = z % sh.nz0, z1 = z / sh.nz0;
       const int row = tm * kBM + quad * 32 + lane;
-      const int n0 = tn * BN;
       const bool row_ok = row < sh.M;
 #ifdef PI0_TIMELINE
       if (threadIdx.x == 64 && idx == (int)blockIdx.x && num_k >= Cfg::kStages) {
@@ -224,47 +279,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       if (threadIdx.x == 64) PI0_STAMP(5);
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
-
-      if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
-        const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
-        constexpr int kChunks = BN / 32 >= 2 ? BN / 64 : 1;  // chunks per half
-#pragma unroll 1
-        for (int c = half * kChunks; c < (BN / 32 >= 2 ? (half + 1) * kChunks : 1 - half); ++c) {
-          const int col0 = n0 + c * 32;
-          if (col0 >= sh.N) break;
-          float v[32];
-          tmem_ld_32x32(taddr + c * 32, v);
-          tmem_ld_wait();
-          if (row_ok) {
-            if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
-            else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
-          }
-        }
-      } else if constexpr (EPI == EPI_GEGLU) {
-        // tile columns [0, BN/2) are gate rows, [BN/2, BN) the matching up rows (interleaved at pack time)
-        const int n_out = sh.N / 2;
-#pragma unroll 1
-        for (int c = half * (BN / 128); c < (half + 1) * (BN / 128); ++c) {
-          const int out_col0 = tn * (BN / 2) + c * 32;
-          if (out_col0 >= n_out) break;
-          float g[32], u[32];
-          tmem_ld_32x32(taddr + c * 32, g);
-          tmem_ld_32x32(taddr + BN / 2 + c * 32, u);
-          tmem_ld_wait();
-          if (row_ok) epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
-        }
-      } else if constexpr (EPI == EPI_ROPE) {
-        static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
-        const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
-#pragma unroll 1
-        for (int c = half * 2; c < half * 2 + 2; ++c) {
-          float x1[32], x2[32];
-          tmem_ld_32x32(taddr + c * 32, x1);
-          tmem_ld_32x32(taddr + 128 + c * 32, x2);
-          tmem_ld_wait();
-          if (row_ok) epi_rope_chunk<bf16>(ep, row, which, tn, c, x1, x2);
-        }
-      }
+      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
@@ -473,6 +488,156 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 }
 
 // ---------------------------------------------------------------------------------------------
+// CTA-pair variant (tcgen05 cta_group::2) for problems with many tiles: a cluster of two CTAs (the two SMs of a TPC)
+// owns a 256 x BN output tile. Each CTA stages ITS 128 rows of A and ITS half (BN/2 rows) of the W tile, so a k-block
+// costs (128 + BN/2) x 64 operand elements per SM instead of (128 + BN) x 64: the L2 -> SM path (~64 B/clk per SM),
+// which caps the single-CTA kernel at 128 x 256 tiles, is relieved by a third and the ring holds 6 stages instead of 4.
+// The leader CTA (cluster rank 0) issues one M = 256 MMA per 16-wide k-step that reads both CTAs' shared memory and
+// writes both CTAs' TMEM (128 accumulator rows each); tcgen05.commit multicasts the "stage free" and "accumulator
+// ready" arrivals to both CTAs, both producers signal their TMA bytes on the LEADER's full barrier, and both CTAs'
+// epilogue warps hand the accumulator buffer back on the leader's barrier.
+// ---------------------------------------------------------------------------------------------
+template <int BN>
+struct Tc2Cfg {
+  static constexpr uint32_t kABytes = kBM * kBK * 2;
+  static constexpr uint32_t kBBytes = (BN / 2) * kBK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 6 : 8;
+  static constexpr int kTmemCols = 2 * BN;
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
+};
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+                    const EpiParams ep) {
+  using Cfg = Tc2Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int n_pairs = gridDim.x >> 1;
+  pdl_trigger();
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);    // leader's producer (arrive + expected bytes of BOTH CTAs); unused in the peer
+      mbar_init(&empty_bar[s], 1);   // one multicast tcgen05.commit per use
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps of each CTA; only the leader's copy is waited on
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_2sm<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / TMA completion can land
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_k = (sh.K + kBK - 1) / kBK;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------
+    if (elect_one()) {
+      const uint32_t full_leader = dsmem_map(smem_u32(&full_bar[0]), 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int idx = pair; idx < sh.total_tiles; idx += n_pairs) {
+        int z, tm, tn;
+        tile_coords(sh, idx, z, tm, tn);
+        const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+        const int a_row = (tm * 2 + rank) * kBM;
+        const int w_row = tn * BN + rank * (BN / 2);
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+          tma_load_4d_2sm(sa, &tmA, full_leader + (uint32_t)(stage * 8), kb * kBK, a_row, z0, z1);
+          tma_load_4d_2sm(sb, &tmB, full_leader + (uint32_t)(stage * 8), kb * kBK, w_row, z0, z1);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) --------------
+    if (rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int idx = pair; idx < sh.total_tiles; idx += n_pairs) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            if (kb == 0) PAIR_STAMP(0, (idx - pair) / n_pairs, 0);
+            if (kb == num_k - 1) PAIR_STAMP(0, (idx - pair) / n_pairs, 1);
+            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+            const uint64_t da = umma_desc_k_sw128(sa);
+            const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k)
+              umma_bf16_2sm(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit_2sm(&empty_bar[stage], 3);
+            if (kb == num_k - 1) umma_commit_2sm(&tfull_bar[acc], 3);
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------ epilogue (both CTAs, own 128 rows) --------
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int idx = pair; idx < sh.total_tiles; idx += n_pairs) {
+      int z, tm, tn;
+      tile_coords(sh, idx, z, tm, tn);
+      const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+      const int row = (tm * 2 + rank) * kBM + quad * 32 + lane;
+      const bool row_ok = row < sh.M;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      if (threadIdx.x == 64) PAIR_STAMP(rank, (idx - pair) / n_pairs, 2);
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
+      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
+      if (threadIdx.x == 64) PAIR_STAMP(rank, (idx - pair) / n_pairs, 3);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // the peer's shared memory and TMEM stay alive until the leader's last MMA has retired
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc_2sm<Cfg::kTmemCols>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -559,6 +724,84 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
+}
+
+// CTA pairs the device can hold at once (148 SMs = 74 TPCs on a full B200; fewer if a GPC has an odd SM out)
+template <int BN, int EPI>
+static int max_active_pairs(int num_sms) {
+  static int cached = 0;
+  if (cached > 0) return cached;
+  using Cfg = Tc2Cfg<BN>;
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = dim3((unsigned)(2 * (num_sms / 2)), 1, 1);
+  lc.blockDim = dim3(kTcThreads, 1, 1);
+  lc.dynamicSmemBytes = Cfg::kSmemBytes;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  lc.attrs = at;
+  lc.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_pair_kernel<BN, EPI>, &lc) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    n = num_sms / 2 - 2;
+  }
+  if (n > num_sms / 2) n = num_sms / 2;
+  cached = n;
+  return n;
+}
+
+template <int BN, int EPI>
+static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  using Cfg = Tc2Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_pair_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, kBM));
+  PI0_TRY(make_map(&tmB, g.W, g.K, g.N, g.nz0, g.nz1, g.ldw, g.w_z0, g.w_z1, BN / 2));
+  TcShape sh;
+  sh.M = g.M; sh.N = g.N; sh.K = g.K; sh.nz0 = g.nz0; sh.nz1 = g.nz1;
+  sh.tiles_m = (g.M + 2 * kBM - 1) / (2 * kBM);   // 256-row tiles, one per CTA pair
+  sh.tiles_n = (g.N + BN - 1) / BN;
+  sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
+  sh.splits = 1;
+  sh.kb_per_split = (g.K + kBK - 1) / kBK;
+  sh.stage_tx = 2 * Cfg::kStageBytes;
+  const int cap = max_active_pairs<BN, EPI>(num_sms);
+  const int pairs = sh.total_tiles < cap ? sh.total_tiles : cap;
+  PI0_CHECK_CUDA(launch_pdl(gemm_tc_pair_kernel<BN, EPI>, dim3((unsigned)(2 * pairs)), dim3(kTcThreads),
+                            Cfg::kSmemBytes, stream, 2, tmA, tmB, sh, g.epi));
+  PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  return 0;
+}
+
+// The CTA-pair kernel pays off once the single-CTA kernel runs several waves of tiles (the regime where the L2 -> SM
+// operand path, not latency, bounds it). PI0_GEMM_PAIR=0 in the environment turns it off (A/B measurements).
+static bool pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PI0_GEMM_PAIR");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+static bool use_pair(const GemmProblem& g, int bn, int num_sms) {
+  if (bn != 256 && !(bn == 128 && g.epi_mode == EPI_STORE)) return false;
+  if (g.M <= kBM) return false;
+  if (g.pair > 0) return true;
+  if (g.pair < 0 || g.splits > 1 || !pair_enabled()) return false;  // an auto-picked split yields to the pair kernel
+  // short-K tiles are epilogue-bound (the 128 x 256 epilogue takes 6-8 us next to a running main loop, a K = 1152 pair
+  // main loop 5 us), where the pair kernel's coarser wave quantisation (72 pairs) costs more than its main loop gains
+  if (g.K < 2048) return false;
+  const long tiles = (long)((g.M + kBM - 1) / kBM) * ((g.N + bn - 1) / bn) * g.nz0 * g.nz1;
+  return tiles >= 4L * num_sms;
 }
 
 // How many clusters of `sp` GEMM CTAs (1 CTA per SM: ~195 KB of shared memory each) the device can hold at once.
@@ -652,6 +895,20 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
     if (sp == 0) sp = auto_s;
   }
   PI0_REQUIRE(sp >= 1 && sp <= 8, "gemm_tc: splits=%d outside [1,8]", sp);
+  if (use_pair(g, bn, num_sms)) {
+    switch (g.epi_mode) {
+      case EPI_STORE:
+        if (bn == 256) return launch_pair<256, EPI_STORE>(g, num_sms, stream);
+        return launch_pair<128, EPI_STORE>(g, num_sms, stream);
+      case EPI_GEGLU:
+        PI0_REQUIRE(g.N % 256 == 0, "gemm_tc: GeGLU N=%d must be a multiple of 256", g.N);
+        return launch_pair<256, EPI_GEGLU>(g, num_sms, stream);
+      case EPI_ROPE:
+        PI0_REQUIRE(g.N == (g.epi.n_q_heads + 2) * 256, "gemm_tc: RoPE epilogue expects N = (q_heads + 2) * 256");
+        return launch_pair<256, EPI_ROPE>(g, num_sms, stream);
+      default: break;  // EPI_EULER is a 32-wide tile: single-CTA kernel below
+    }
+  }
   switch (g.epi_mode) {
     case EPI_STORE:
       switch (bn) {
@@ -681,8 +938,12 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
 
 // development aid (not part of the C ABI in include/pi0b200.h): cluster capacity the tile picker works with
 extern "C" int pi0_debug_max_clusters(int sp) { return pi0::max_active_clusters(sp, 148); }
+extern "C" int pi0_debug_max_pairs(void) { return pi0::max_active_pairs<256, pi0::EPI_STORE>(148); }
 
 #ifdef PI0_TIMELINE
+extern "C" int pi0_debug_pair_timeline(unsigned long long* out) {
+  return cudaMemcpyFromSymbol(out, pi0::g_pair_timeline, sizeof(pi0::g_pair_timeline)) == cudaSuccess ? 0 : -1;
+}
 extern "C" int pi0_debug_timeline(unsigned long long* out) {
   return cudaMemcpyFromSymbol(out, pi0::g_timeline, sizeof(pi0::g_timeline)) == cudaSuccess ? 0 : -1;
 }

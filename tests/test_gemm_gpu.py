@@ -164,6 +164,91 @@ def test_gemm_batched_splitk(cuda):
     assert (sc[:, :, :Kk].float() - ref).abs().max().item() <= 3e-2 * ref.abs().max().item()
 
 
+# ---- CTA-pair kernel (tcgen05 cta_group::2): impl 3 forces it, impl 2 forbids it -----------------------------------------
+@pytest.mark.parametrize("M,N,K,bn", [(256, 256, 64, 256), (1000, 768, 1152, 256), (2304, 4304, 1152, 256),
+                                      (700, 1152, 4304, 128), (130, 520, 192, 256), (4096, 2048, 2048, 128)])
+def test_gemm_pair_matches_single_cta(cuda, M, N, K, bn):
+    """Same tile arithmetic on one SM or on a CTA pair: bias + activation + residual epilogue, ragged M / N / K tails,
+    several tiles per pair (persistent loop, both TMEM accumulator buffers, ring wrap-around)."""
+    A = _rand((M, K), cuda, seed=51)
+    W = _rand((N, K), cuda, 0.03, seed=52)
+    bias = _rand((N,), cuda, 0.5, torch.float32, seed=53)
+    res = _rand((M, N), cuda, seed=54)
+    o_pair = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    o_one = torch.zeros_like(o_pair)
+    pb.gemm(A, W, o_pair, bias=bias, res=res, act=pb.ACT_GELU_TANH, bn=bn, impl=3)
+    pb.gemm(A, W, o_one, bias=bias, res=res, act=pb.ACT_GELU_TANH, bn=bn, impl=2)
+    torch.cuda.synchronize()
+    lin = (_ref_linear(A, W) + bias).bfloat16().float()
+    ref = (torch.nn.functional.gelu(lin, approximate="tanh").bfloat16().float() + res.float()).bfloat16().float()
+    scale = max(1.0, ref.abs().max().item())
+    assert (o_pair.float() - ref).abs().max().item() <= 3e-2 * scale
+    assert (o_pair.float() - o_one.float()).abs().max().item() <= 2 ** -6 * scale
+
+
+def test_gemm_pair_few_sms(cuda):
+    """A grid of 2 pairs walks 40 tiles: exercises the persistent tile loop and accumulator hand-back far past one wave."""
+    M, N, K = 1280, 2048, 512
+    A = _rand((M, K), cuda, seed=55)
+    W = _rand((N, K), cuda, 0.03, seed=56)
+    out = torch.zeros((M, N), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(A, W, out, bn=256, impl=3, num_sms=4)
+    torch.cuda.synchronize()
+    ref = _ref_linear(A, W)
+    assert (out.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item() + 1e-3
+
+
+def test_gemm_pair_geglu(cuda):
+    M, K, inter = 1500, 1024, 2048
+    A = _rand((M, K), cuda, seed=57)
+    Wg = _rand((inter, K), cuda, 0.03, seed=58)
+    Wu = _rand((inter, K), cuda, 0.03, seed=59)
+    Wgu = torch.stack([Wg.view(-1, 128, K), Wu.view(-1, 128, K)], dim=1).reshape(2 * inter, K).contiguous()
+    out = torch.zeros((M, inter), dtype=torch.bfloat16, device=cuda)
+    one = torch.zeros_like(out)
+    pb.gemm(A, Wgu, out, epi_mode=pb.EPI_GEGLU, bn=256, impl=3)
+    pb.gemm(A, Wgu, one, epi_mode=pb.EPI_GEGLU, bn=256, impl=2)
+    torch.cuda.synchronize()
+    g = _ref_linear(A, Wg).bfloat16().float()
+    u = _ref_linear(A, Wu).bfloat16().float()
+    ref = (torch.nn.functional.gelu(g, approximate="tanh").bfloat16().float() * u).bfloat16().float()
+    scale = max(1.0, ref.abs().max().item())
+    assert (out.float() - ref).abs().max().item() <= 3e-2 * scale
+    assert (out.float() - one.float()).abs().max().item() <= 2 ** -6 * scale
+
+
+def test_gemm_pair_rope_qkv(cuda):
+    """Fused q|k|v projection with the RoPE / KV-cache epilogue: the pair kernel writes the same q, K cache and V^T cache
+    as the single-CTA kernel (which the end-to-end tests pin against the oracle)."""
+    B, T, hid, heads = 3, 328, 512, 8
+    M, N = B * T, (heads + 2) * 256
+    A = _rand((M, hid), cuda, seed=60)
+    W = _rand((N, hid), cuda, 0.05, seed=61)
+    pos = (torch.arange(M, device=cuda, dtype=torch.int32) % T).contiguous()
+    inv = 1.0 / (10000.0 ** (torch.arange(0, 128, device=cuda, dtype=torch.float32) / 128.0))
+    ang = torch.arange(T, device=cuda, dtype=torch.float32)[:, None] * inv[None, :]
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    kv_pitch, vt_pitch = 336, 336
+    outs = []
+    for impl in (3, 2):
+        q = torch.zeros((M, heads * 256), dtype=torch.bfloat16, device=cuda)
+        kc = torch.zeros((B, kv_pitch, 256), dtype=torch.bfloat16, device=cuda)
+        vt = torch.zeros((B, 256, vt_pitch), dtype=torch.bfloat16, device=cuda)
+        pb.gemm(A, W, q, epi_mode=pb.EPI_ROPE, bn=256, impl=impl, ldc=heads * 256, rope_cos=cos, rope_sin=sin,
+                pos_ids=pos, kcache=kc, n_q_heads=heads, kv_pitch=kv_pitch, vt=vt, vt_pitch=vt_pitch, vt_rpb=T, vt_toff=0)
+        torch.cuda.synchronize()
+        outs.append((q, kc, vt))
+    lin = _ref_linear(A, W).bfloat16().float().view(B, T, heads + 2, 256)
+    c, s_ = cos[None, :, None, :], sin[None, :, None, :]
+    x1, x2 = lin[..., :128], lin[..., 128:]
+    rot = torch.cat([x1 * c - x2 * s_, x2 * c + x1 * s_], dim=-1).bfloat16().float()
+    assert (outs[0][0].float().view(B, T, heads, 256) - rot[:, :, :heads]).abs().max().item() <= 5e-2
+    assert (outs[0][1][:, :T].float() - rot[:, :, heads]).abs().max().item() <= 5e-2
+    assert (outs[0][2][:, :, :T].float() - lin[:, :, heads + 1].transpose(1, 2)).abs().max().item() <= 5e-2
+    for a, b in zip(outs[0], outs[1]):
+        assert (a.float() - b.float()).abs().max().item() <= 2 ** -6 * max(1.0, b.float().abs().max().item())
+
+
 def test_gemm_tc_throughput_report(cuda):
     """Not an assertion on speed: prints achieved TFLOP/s of the tcgen05 kernel for the log."""
     M, N, K = 8192, 8192, 2048
