@@ -840,7 +840,8 @@ int max_active_clusters(int sp, int num_sms) {
 // whatever the tile width; wide tiles are MMA-bound (0.47 us per 128x256x64 k-block under the power cap). A persistent launch
 // (splits == 1) pays the CTA setup once. Split factors are thread-block cluster sizes (<= 8); every rank must own
 // >= 2 k-blocks; the reduction moves rows x 32 x 4 B per chunk and rank over distributed shared memory.
-void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* bn_io, int* splits_out) {
+void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* bn_io, int* splits_out,
+                  bool rope_epilogue = false) {
   const int tm = (M + kBM - 1) / kBM;
   const int num_k = (K + kBK - 1) / kBK;
   const int rows = M < kBM ? M : kBM;
@@ -854,8 +855,10 @@ void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* 
     if (fixed_bn && bn != *bn_io) continue;
     if (!fixed_bn && bn > 64 && N < bn) continue;
     const long tiles = (long)tm * ((N + bn - 1) / bn) * nz;
-    const double t_epi = 0.3 * bn / 64.0;
-    for (int sp = 1; sp <= 8; ++sp) {
+    // the RoPE / KV-cache epilogue costs ~4x a plain store per tile (measured: denoise q|k|v at M = 320, 30 tiles: 20 us
+    // unsplit, 15 us as clusters of 4 that share the epilogue; clusters of 8 lose again to the reduction)
+    const double t_epi = (rope_epilogue ? 1.2 : 0.3) * bn / 64.0;
+    for (int sp = 1; sp <= (rope_epilogue ? 4 : 8); ++sp) {
       if (sp > 1 && num_k / sp < 2) break;
       const int per = (num_k + sp - 1) / sp;
       double cost;
@@ -891,7 +894,7 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   if (sp == 0 || bn == 0) {
     int auto_s = 1;
     const bool fixed = bn != 0;
-    gemm_tc_pick(g.M, g.N, g.K, g.nz0 * g.nz1, num_sms, fixed, &bn, &auto_s);
+    gemm_tc_pick(g.M, g.N, g.K, g.nz0 * g.nz1, num_sms, fixed, &bn, &auto_s, g.epi_mode == EPI_ROPE);
     if (sp == 0) sp = auto_s;
   }
   PI0_REQUIRE(sp >= 1 && sp <= 8, "gemm_tc: splits=%d outside [1,8]", sp);
