@@ -101,9 +101,11 @@ __device__ __forceinline__ int64_t epi_out_row(const EpiParams& ep, int row) {
 // Written as whole-chunk passes: every feature test is one uniform branch per 32-column chunk and every pass is a
 // straight-line loop over 32 independent elements, so a single epilogue warp per scheduler keeps its ALU pipe
 // busy (the element-at-a-time form was latency-bound at ~300 cycles per element).
+// direct_store == false: stop after the arithmetic (v[] then holds the final values, to be rounded by the caller's pack);
+// used by the tcgen05 kernels' TMA-store path, which never sees a transposed-V region.
 template <typename T>
 __device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, int col0, int N, int64_t zoff,
-                                                float* v) {
+                                                float* v, bool direct_store = true) {
   if (col0 >= ep.vt_col0) {  // V^T region: lanes of a warp hold consecutive t => coalesced per d
     const int b = row / ep.vt_rpb, t = row % ep.vt_rpb;
     T* vt = reinterpret_cast<T*>(ep.vt);
@@ -172,6 +174,7 @@ __device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, in
       }
     }
   }
+  if (!direct_store) return;
   T* out = reinterpret_cast<T*>(ep.out) + zoff + epi_out_row(ep, row) * ep.ldc + col0;
 #pragma unroll
   for (int g = 0; g < 4; ++g)
@@ -194,6 +197,16 @@ __device__ __forceinline__ void epi_geglu_chunk(const EpiParams& ep, int row, in
       t[j] = a * u;
     }
     store8<T>(out + g * 8, t);
+  }
+}
+
+// arithmetic only (TMA-store path): gate[j] <- rnd(gelu(rnd(gate))) * rnd(up), rounded by the caller's pack
+template <typename T>
+__device__ __forceinline__ void epi_geglu_math(float* gate, const float* up) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float a = Num<T>::rnd(Num<T>::gelu(Num<T>::rnd(gate[j])));
+    gate[j] = a * Num<T>::rnd(up[j]);
   }
 }
 

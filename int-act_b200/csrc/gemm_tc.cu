@@ -27,6 +27,11 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGroupM = 8;
 constexpr int kTcThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps (2 per TMEM lane quadrant)
+// TMA-store staging: every epilogue warp owns two 32-row x 64-byte (one 32-column bf16 chunk) buffers, written in the
+// 64-byte-swizzle pattern of the output tensor map (16-byte piece g of row r lands at piece g ^ ((r >> 1) & 3): the
+// row-per-lane st.shared.v4 is then bank-conflict free) and drained by cp.async.bulk.tensor stores.
+constexpr uint32_t kStoreBufBytes = 32 * 64;
+constexpr uint32_t kStoreStageBytes = 8 * 2 * kStoreBufBytes;
 
 template <int BN>
 struct TcCfg {
@@ -36,6 +41,8 @@ struct TcCfg {
   static constexpr int kStages = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
   static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
   static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  // persistent kernel: + the epilogue warps' TMA-store staging buffers behind the (1 KiB padded) barrier block
+  static constexpr uint32_t kSmemBytesStaged = kStages * kStageBytes + 1024 + 1024 + kStoreStageBytes;
 };
 
 struct TcShape {
@@ -46,6 +53,7 @@ struct TcShape {
   int splits;        // split-K: CTAs (= cluster size) per output tile, 1 = none
   int kb_per_split;  // k-blocks (of kBK) per split
   uint32_t stage_tx; // bytes one pipeline stage receives: A box (rows clipped to M for a single short M tile) + W box
+  int tma_store;     // 1: EPI_STORE / EPI_GEGLU output goes through shared memory and tensor-map stores (tmC valid)
 };
 
 __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, int& tm, int& tn) {
@@ -64,10 +72,41 @@ __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, 
 // Epilogue of one 128-row accumulator tile: TMEM lanes of this warp's quadrant -> registers -> fused epilogue -> global.
 // `part` selects which of the NPARTS slices of the tile's column chunks this warp drains (NPARTS warps share a lane
 // quadrant).
+// One 32-row x 32-column bf16 chunk of this warp (lane = row) -> swizzled staging buffer -> TMA store at (x, y, z0, z1).
+// Rows >= M and columns >= N are clipped by the tensor map. `sbuf` alternates between the warp's two buffers: before a
+// buffer is rewritten, the store issued from it two chunks ago must have finished READING it (wait_group.read 1).
+__device__ __forceinline__ void stage_and_store(const CUtensorMap* tmC, uint8_t* stage2, int& sbuf, const float* v, int x,
+                                                int y, int z0, int z1) {
+  const int lane = threadIdx.x & 31;
+  uint8_t* buf = stage2 + sbuf * kStoreBufBytes;
+  sbuf ^= 1;
+  if (lane == 0) bulk_wait_read<1>();
+  __syncwarp();
+  uint8_t* mine = buf + lane * 64;
+  const int sw = (lane >> 1) & 3;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    uint4 pk;
+    pk.x = bf16x2_bits(v[g * 8 + 1], v[g * 8 + 0]);
+    pk.y = bf16x2_bits(v[g * 8 + 3], v[g * 8 + 2]);
+    pk.z = bf16x2_bits(v[g * 8 + 5], v[g * 8 + 4]);
+    pk.w = bf16x2_bits(v[g * 8 + 7], v[g * 8 + 6]);
+    *reinterpret_cast<uint4*>(mine + ((g ^ sw) << 4)) = pk;
+  }
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_4d(tmC, buf, x, y, z0, z1);
+    bulk_commit();
+  }
+}
+
 template <int BN, int EPI, int NPARTS = 2>
 __device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& ep, uint32_t taddr, int row, bool row_ok,
-                                           int tn, int z0, int z1, int part) {
+                                           int tn, int z0, int z1, int part, const CUtensorMap* tmC, uint8_t* stage2,
+                                           int& sbuf) {
   const int n0 = tn * BN;
+  const int row0 = row - (int)(threadIdx.x & 31);
   if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
     const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
     constexpr int kTotal = BN / 32;
@@ -79,9 +118,15 @@ __device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& e
       float v[32];
       tmem_ld_32x32(taddr + c * 32, v);
       tmem_ld_wait();
-      if (row_ok) {
-        if constexpr (EPI == EPI_STORE) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
-        else epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
+      if constexpr (EPI == EPI_STORE) {
+        if (sh.tma_store) {
+          if (row_ok) epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v, false);
+          stage_and_store(tmC, stage2, sbuf, v, col0, row0, z0, z1);
+        } else if (row_ok) {
+          epi_store_chunk<bf16>(ep, row, col0, sh.N, zoff, v);
+        }
+      } else {
+        if (row_ok) epi_euler_chunk<bf16>(ep, row, col0, sh.N, v);
       }
     }
   } else if constexpr (EPI == EPI_GEGLU) {
@@ -97,7 +142,12 @@ __device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& e
       tmem_ld_32x32(taddr + c * 32, g);
       tmem_ld_32x32(taddr + BN / 2 + c * 32, u);
       tmem_ld_wait();
-      if (row_ok) epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
+      if (sh.tma_store) {
+        epi_geglu_math<bf16>(g, u);
+        stage_and_store(tmC, stage2, sbuf, g, out_col0, row0, z0, z1);
+      } else if (row_ok) {
+        epi_geglu_chunk<bf16>(ep, row, out_col0, n_out, g, u);
+      }
     }
   } else if constexpr (EPI == EPI_ROPE) {
     static_assert(EPI != EPI_ROPE || BN == 256, "RoPE epilogue needs one 256-wide head per tile");
@@ -116,7 +166,8 @@ __device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& e
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kTcThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmC, const TcShape sh,
                const EpiParams ep) {
   using Cfg = TcCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -260,6 +311,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------ epilogue ----------------------------------
     const int quad = warp & 3;          // TMEM lanes [32*quad, 32*quad+32) are the ones this warp may read
     const int half = (warp - 2) >> 2;   // which half of the tile's columns this warp drains
+    uint8_t* stage2 = reinterpret_cast<uint8_t*>(full_bar) + 1024 + (warp - 2) * 2 * kStoreBufBytes;
+    int sbuf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
@@ -279,7 +332,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       if (threadIdx.x == 64) PI0_STAMP(5);
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
-      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half);
+      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half, &tmC, stage2, sbuf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
@@ -287,6 +340,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (sh.tma_store && lane == 0) bulk_wait_all();  // this warp's output stores have landed before the CTA exits
   }
 
   tc_fence_before();
@@ -504,12 +558,13 @@ struct Tc2Cfg {
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 6 : 8;
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 1024 + kStoreStageBytes;
 };
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kTcThreads, 1)
-gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const TcShape sh,
                     const EpiParams ep) {
   using Cfg = Tc2Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -530,6 +585,7 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (sh.tma_store) tma_prefetch_desc(&tmC);
     for (int s = 0; s < Cfg::kStages; ++s) {
       mbar_init(&full_bar[s], 1);    // leader's producer (arrive + expected bytes of BOTH CTAs); unused in the peer
       mbar_init(&empty_bar[s], 1);   // one multicast tcgen05.commit per use
@@ -609,6 +665,8 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ------------------------------ epilogue (both CTAs, own 128 rows) --------
     const int quad = warp & 3;
     const int half = (warp - 2) >> 2;
+    uint8_t* stage2 = reinterpret_cast<uint8_t*>(full_bar) + 1024 + (warp - 2) * 2 * kStoreBufBytes;
+    int sbuf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int idx = pair; idx < sh.total_tiles; idx += n_pairs) {
@@ -621,7 +679,7 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tc_fence_after();
       if (threadIdx.x == 64) PAIR_STAMP(rank, (idx - pair) / n_pairs, 2);
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
-      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half);
+      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half, &tmC, stage2, sbuf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
@@ -629,6 +687,7 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (sh.tma_store && lane == 0) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -659,7 +718,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // rank-4 bf16 tensor map {k, rows, z0, z1}, box {64, box_rows, 1, 1}, 128 B swizzle, zero OOB fill
 static int make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0,
-                    int64_t sz1, int box_rows) {
+                    int64_t sz1, int box_rows, int box_k = kBK, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = get_encode_fn();
   PI0_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
   PI0_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA operand base %p not 16-byte aligned", base);
@@ -670,14 +729,36 @@ static int make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0
   cuuint64_t s3 = nz1 > 1 ? (cuuint64_t)sz1 * 2 : s1;
   PI0_REQUIRE(s2 % 16 == 0 && s3 % 16 == 0, "TMA batch strides must be multiples of 8 elements");
   cuuint64_t gstride[3] = {s1, s2, s3};
-  cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)box_k, (cuuint32_t)box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PI0_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d): K=%d rows=%d nz=%dx%d ld=%lld", (int)r, K, rows,
               nz0, nz1, (long long)ld);
   return 0;
+}
+
+// Output tensor map of the TMA-store epilogue ({columns, rows, z0, z1}, 32 x 32 box, 64-byte swizzle) when the epilogue
+// writes a plain row-major bf16 matrix: EPI_STORE without row remap / transposed-V region, or EPI_GEGLU. Returns 1 when
+// `map` is valid, 0 when the kernel must keep its direct stores, < 0 on error.
+static int make_out_map(CUtensorMap* map, const GemmProblem& g) {
+  const bool store = g.epi_mode == EPI_STORE && g.epi.rpb_in <= 0 && (g.epi.vt == nullptr || g.epi.vt_col0 >= g.N);
+  const bool geglu = g.epi_mode == EPI_GEGLU && g.epi.rpb_in <= 0;
+  if (!store && !geglu) return 0;
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("PI0_TMA_STORE");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (!enabled) return 0;
+  const int n_out = geglu ? g.N / 2 : g.N;
+  const int64_t z0 = g.nz0 > 1 ? g.epi.out_z0 : 0, z1 = g.nz1 > 1 ? g.epi.out_z1 : 0;
+  if ((reinterpret_cast<uintptr_t>(g.epi.out) & 15) != 0 || (g.epi.ldc * 2) % 16 != 0 || (z0 * 2) % 16 != 0 ||
+      (z1 * 2) % 16 != 0 || g.epi.ldc < n_out)
+    return 0;
+  PI0_TRY(make_map(map, g.epi.out, n_out, g.M, g.nz0, g.nz1, g.epi.ldc, z0, z1, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B));
+  return 1;
 }
 
 template <int BN, int EPI>
@@ -686,7 +767,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   static bool attr_set = false;
   if (!attr_set) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)Cfg::kSmemBytes));
+                                        (int)Cfg::kSmemBytesStaged));
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_splitk_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytes));
     attr_set = true;
@@ -706,6 +787,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   sh.splits = 1;
   sh.kb_per_split = num_k;
   sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
+  sh.tma_store = 0;
   if (splits > 1) {
     // every rank of the cluster must own at least one k-block
     int per = (num_k + splits - 1) / splits;
@@ -718,8 +800,12 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
                               dim3(kTcThreads), Cfg::kSmemBytes, stream, sh.splits, tmA, tmB, sh, g.epi));
   } else {
     int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
-    PI0_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcThreads), Cfg::kSmemBytes, stream,
-                              1, tmA, tmB, sh, g.epi));
+    CUtensorMap tmC = tmA;
+    const int have_c = make_out_map(&tmC, g);
+    if (have_c < 0) return have_c;
+    sh.tma_store = have_c;
+    PI0_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcThreads), Cfg::kSmemBytesStaged,
+                              stream, 1, tmA, tmB, tmC, sh, g.epi));
   }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
@@ -773,10 +859,14 @@ static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   sh.splits = 1;
   sh.kb_per_split = (g.K + kBK - 1) / kBK;
   sh.stage_tx = 2 * Cfg::kStageBytes;
+  CUtensorMap tmC = tmA;
+  const int have_c = make_out_map(&tmC, g);
+  if (have_c < 0) return have_c;
+  sh.tma_store = have_c;
   const int cap = max_active_pairs<BN, EPI>(num_sms);
   const int pairs = sh.total_tiles < cap ? sh.total_tiles : cap;
   PI0_CHECK_CUDA(launch_pdl(gemm_tc_pair_kernel<BN, EPI>, dim3((unsigned)(2 * pairs)), dim3(kTcThreads),
-                            Cfg::kSmemBytes, stream, 2, tmA, tmB, sh, g.epi));
+                            Cfg::kSmemBytes, stream, 2, tmA, tmB, tmC, sh, g.epi));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
