@@ -887,9 +887,16 @@ static bool use_pair(const GemmProblem& g, int bn, int num_sms) {
   if (g.M <= kBM) return false;
   if (g.pair > 0) return true;
   if (g.pair < 0 || g.splits > 1 || !pair_enabled()) return false;  // an auto-picked split yields to the pair kernel
-  // short-K tiles are epilogue-bound (the 128 x 256 epilogue takes 6-8 us next to a running main loop, a K = 1152 pair
-  // main loop 5 us), where the pair kernel's coarser wave quantisation (72 pairs) costs more than its main loop gains
-  if (g.K < 2048) return false;
+  // Very short K makes a tile epilogue-bound (a 128 x 256 bias + GELU epilogue takes ~6 us next to a running main loop, a
+  // K = 1152 pair main loop 5.3 us) and the pair's coarser wave quantisation (72 slots) then costs more than its main loop
+  // gains: measured break-even near K = 1024 with the TMA-store epilogue (SigLIP tower 18.2 -> 17.5 ms at batch 64 with
+  // its K = 1152 GEMMs on the pair kernel). PI0_PAIR_MIN_K overrides.
+  static int min_k = -1;
+  if (min_k < 0) {
+    const char* e = getenv("PI0_PAIR_MIN_K");
+    min_k = e ? atoi(e) : 1024;
+  }
+  if (g.K < min_k) return false;
   const long tiles = (long)((g.M + kBM - 1) / kBM) * ((g.N + bn - 1) / bn) * g.nz0 * g.nz1;
   return tiles >= 4L * num_sms;
 }
