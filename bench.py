@@ -218,6 +218,7 @@ def label_flops(label, B, n_cams, lang_len, horizon):
         "prefill.gateup_geglu": 2 * Mg * 32768 * 2048, "prefill.down": 2 * Mg * 2048 * 16384,
         "prefill.qkv_rope": 2 * Mg * 2560 * 2048, "prefill.o_proj": 2 * Mg * 2048 * 2048,
         "prefill.scores": 2 * B * P * 8 * P * 256, "prefill.pv": 2 * B * P * 8 * P * 256,
+        "prefill.attention": 4 * B * P * 8 * P * 256,
         "siglip.qkv": 2 * Ms * 3456 * 1152, "siglip.out_proj": 2 * Ms * 1152 * 1152,
         "siglip.fc1_gelu": 2 * Ms * 4304 * 1152, "siglip.fc2": 2 * Ms * 4304 * 1152,
         "siglip.scores": 2 * B * 16 * 256 * 256 * 72, "siglip.pv": 2 * B * 16 * 256 * 256 * 72,

@@ -198,6 +198,12 @@ int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vt
  * probabilities.
  * Replaces HF SiglipAttention's matmul / softmax / matmul ([mirror] src/model/mvla/mllm.py:182-187). */
 int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream);
+/* Fused prefix-prefill attention on tcgen05 (bf16, attn_prefill.cu): q / att [B*T, 8*256] (8 query heads per token against
+ * one K / V, MQA), kcache [B, kv_pitch, 256], vtcache [B, 256, vt_pitch], pad [B, P] (key j visible iff pad[b][j]);
+ * scores = rnd(rnd(q.k) * 256^-0.5), finite mask value, fp32 softmax, bf16 probabilities, P <= 336, P % 8 == 0.
+ * Replaces eager_attention_forward of the prefix pass ([mirror] src/model/mvla/mllm.py:265-317). */
+int pi0_prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B,
+                          int T, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
 

@@ -101,6 +101,8 @@ SIGNATURES = {
     "pi0_decode_attention": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.c_int, c_ptr]),
     "pi0_siglip_attention": (C.c_int, [c_ptr, c_ptr, C.c_int, c_ptr]),
+    "pi0_prefill_attention": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                        C.c_int, c_ptr]),
     "pi0_decode_attention_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                              C.c_int, c_ptr]),
     "pi0_decode_attention_split": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,

@@ -66,6 +66,12 @@ int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache,
   return decode_attention(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch, num_sms, (cudaStream_t)stream);
 }
 
+int pi0_prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B,
+                          int T, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream) {
+  return prefill_attention(q, kcache, vtcache, att, pad, B, T, P, kv_pitch, vt_pitch, num_sms > 0 ? num_sms : 148,
+                           (cudaStream_t)stream);
+}
+
 int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream) {
   return siglip_attention(qkv, att, B, (cudaStream_t)stream);
 }

@@ -37,6 +37,10 @@ int decode_attention_batch(const void* q, const void* kcache, const void* vtcach
 
 // fused SigLIP self-attention (attn_siglip.cu), bf16 only: fused q|k|v [B*256, 3456] -> att [B*256, 1152]
 int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s);
+// fused prefix-prefill attention on tcgen05 (attn_prefill.cu); q / att [B*T][8*256], P <= 336 prefix keys
+bool prefill_attention_supported(int T, int P);
+int prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B, int T,
+                      int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);
 
 // weight-streaming mma.sync GEMMs for M <= 16 suffix rows (gemm_skinny.cu), bf16 only
 bool skinny_supported(int M);

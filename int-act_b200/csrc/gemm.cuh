@@ -36,6 +36,9 @@ inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64
 int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStream_t stream);
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream);
+// rank-4 bf16 tensor map {k, rows, z0, z1} with box {box_k, box_rows, 1, 1}, 64- or 128-byte swizzle, zero OOB fill
+int tc_make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0, int64_t sz1,
+                int box_rows, int box_k, int swizzle_bytes);
 template <typename T>
 int gemm_simt_launch(const GemmProblem& g, cudaStream_t stream);
 

@@ -66,6 +66,7 @@ struct pi0_ctx {
   int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
+  bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
   Buf bufs[40];
   int nbufs;
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
@@ -300,6 +301,15 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     else
       PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
                                c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+  } else if (!suffix && c->prefill_fused && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 &&
+             prefill_attention_supported(T, c->P) &&
+             (int64_t)B * ((T * kHeads + 127) / 128) >= 2 * (c->cfg.num_sms > 0 ? c->cfg.num_sms : 148)) {
+    // prefix pass, bf16, rollout batches (>= 2 waves of 128-row tiles): scores + masked softmax + P.V of a layer in one
+    // tcgen05 launch. A tile is a serial S -> softmax -> P.V chain of ~19 us, so with fewer tiles than SMs (batch 1: 21
+    // tiles) the three-launch GEMM chain, which spreads the same work over every SM, is faster (2.30 vs 2.55 ms prefill)
+    PROF("prefill.attention");
+    PI0_TRY(prefill_attention(q, kc, vt, att, c->pad, B, T, c->P, c->kv_pitch, c->vt_pitch,
+                              c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
   } else {
   // scores[b, t*8+h, j] = rnd(rnd(q . k) * 256^-0.5)   (MQA: the 8 heads of a token are 8 rows against one K)
   {
@@ -392,6 +402,8 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
     c->attn_split = !(e && strcmp(e, "0") == 0);
     const char* f = getenv("PI0_SIGLIP_FUSED");
     c->siglip_fused = !(f && strcmp(f, "0") == 0);
+    const char* pf = getenv("PI0_PREFILL_FUSED");
+    c->prefill_fused = !(pf && strcmp(pf, "0") == 0);
   }
   const char* mega_env = getenv("PI0_MEGA");
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;

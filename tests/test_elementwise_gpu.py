@@ -198,3 +198,33 @@ def test_siglip_attention_fused(cuda, B):
     ref = (pr @ v.float()).bfloat16().float().transpose(1, 2).reshape(B * T, H * D)
     err = (att.float().cpu() - ref).abs().max().item()
     assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,T,P,pitch", [(1, 328, 328, 336), (3, 328, 328, 333 + 3), (2, 72, 72, 80), (2, 130, 136, 144)])
+def test_prefill_attention_fused(cuda, B, T, P, pitch):
+    """Fused tcgen05 prefix attention (attn_prefill.cu) against a torch restatement with the reference's rounding
+    points: bf16 scores scaled by 256^-0.5, key mask with the finite mask value, fp32 softmax, bf16 probabilities, bf16
+    output. MQA: 8 query heads per token against one K / V; ragged tiles (T * 8 not a multiple of 128), padded keys,
+    stale suffix rows behind the prefix keys in both caches, a fully padded key range and rows whose token is itself pad.
+    T <= P: the queries are the first T prefix tokens."""
+    g = torch.Generator().manual_seed(11)
+    q = (torch.randn((B * T, 8 * 256), generator=g) * 0.8).bfloat16()
+    kc = torch.randn((B, pitch, 256), generator=g).bfloat16()           # rows >= P: stale data that must not be read
+    vt = torch.randn((B, 256, pitch), generator=g).bfloat16()
+    pad = torch.ones((B, P), dtype=torch.uint8)
+    pad[0, P - 17:] = 0                                                 # right-padded language tokens
+    if B > 1:
+        pad[1, 5:40] = 0
+    att = torch.full((B * T, 8 * 256), 7.0, dtype=torch.bfloat16, device=cuda)
+    dq, dk, dv, dp = q.to(cuda), kc.to(cuda), vt.to(cuda), pad.to(cuda)
+    pb.check(pb.lib().pi0_prefill_attention(pb.ptr(dq), pb.ptr(dk), pb.ptr(dv), pb.ptr(att), pb.ptr(dp), B, T, P, pitch,
+                                            pitch, 148, _stream()), "pi0_prefill_attention")
+    torch.cuda.synchronize()
+    qf = q.float().view(B, T * 8, 256)
+    sc = (qf @ kc[:, :P].float().transpose(1, 2)).bfloat16().float()
+    sc = (sc * 0.0625).bfloat16().float()
+    sc = torch.where(pad[:, None, :].bool(), sc, torch.tensor(-2.3819763e38))
+    pr = torch.softmax(sc, dim=-1).bfloat16().float()
+    ref = (pr @ vt[:, :, :P].float().transpose(1, 2)).bfloat16().float().view(B * T, 8 * 256)
+    err = (att.float().cpu() - ref).abs().max().item()
+    assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
