@@ -87,6 +87,15 @@ def test_rollout_batch_split_attention_parity(cuda):
     assert (out - ref).abs().max().item() <= TOL["bf16"]
 
 
+def test_rollout_batch_fused_prefix_attention_parity(cuda):
+    """Batch 16 (>= 2 waves of 128-row tiles): the prefix pass runs the fused tcgen05 attention (attn_prefill.cu) and the
+    CTA-pair GEMMs; ragged text lengths so the key mask matters, 3 Gemma layers so a KV-only last layer follows a full
+    one."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=3, vocab=1024)
+    eng, out, ref, _, _ = _run(cuda, dims, "bf16", B=16, n_valid_text=[72, 9, 33, 2, 50, 17, 64, 1])
+    assert (out - ref).abs().max().item() <= TOL["bf16"]
+
+
 def test_two_cameras_long_horizon(cuda):
     """LIBERO-shaped (BASELINE config 5): 2 cameras, horizon 16 -> P = 584, S = 17."""
     dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=1024)

@@ -200,13 +200,15 @@ def test_siglip_attention_fused(cuda, B):
     assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
 
 
-@pytest.mark.parametrize("B,T,P,pitch", [(1, 328, 328, 336), (3, 328, 328, 333 + 3), (2, 72, 72, 80), (2, 130, 136, 144)])
-def test_prefill_attention_fused(cuda, B, T, P, pitch):
+@pytest.mark.parametrize("B,T,P,pitch,sms", [(1, 328, 328, 336, 148), (3, 328, 328, 333 + 3, 148), (2, 72, 72, 80, 148),
+                                             (2, 130, 136, 144, 148), (3, 328, 328, 336, 5), (5, 200, 208, 216, 3)])
+def test_prefill_attention_fused(cuda, B, T, P, pitch, sms):
     """Fused tcgen05 prefix attention (attn_prefill.cu) against a torch restatement with the reference's rounding
     points: bf16 scores scaled by 256^-0.5, key mask with the finite mask value, fp32 softmax, bf16 probabilities, bf16
     output. MQA: 8 query heads per token against one K / V; ragged tiles (T * 8 not a multiple of 128), padded keys,
     stale suffix rows behind the prefix keys in both caches, a fully padded key range and rows whose token is itself pad.
-    T <= P: the queries are the first T prefix tokens."""
+    T <= P: the queries are the first T prefix tokens. sms < tiles: the persistent loop (TMEM / barrier phases, staging
+    buffers aliased with the P tile) over many tiles per CTA, across sample boundaries."""
     g = torch.Generator().manual_seed(11)
     q = (torch.randn((B * T, 8 * 256), generator=g) * 0.8).bfloat16()
     kc = torch.randn((B, pitch, 256), generator=g).bfloat16()           # rows >= P: stale data that must not be read
@@ -218,7 +220,7 @@ def test_prefill_attention_fused(cuda, B, T, P, pitch):
     att = torch.full((B * T, 8 * 256), 7.0, dtype=torch.bfloat16, device=cuda)
     dq, dk, dv, dp = q.to(cuda), kc.to(cuda), vt.to(cuda), pad.to(cuda)
     pb.check(pb.lib().pi0_prefill_attention(pb.ptr(dq), pb.ptr(dk), pb.ptr(dv), pb.ptr(att), pb.ptr(dp), B, T, P, pitch,
-                                            pitch, 148, _stream()), "pi0_prefill_attention")
+                                            pitch, sms, _stream()), "pi0_prefill_attention")
     torch.cuda.synchronize()
     qf = q.float().view(B, T * 8, 256)
     sc = (qf @ kc[:, :P].float().transpose(1, 2)).bfloat16().float()
