@@ -23,8 +23,9 @@ namespace pi0 {
 
 namespace {
 
-constexpr int kPfThreads = 448;            // TMA warp, MMA warp, 12 softmax / epilogue warps (3 per TMEM lane quadrant)
-constexpr int kPfParts = 3;                // column parts of the softmax: 4 chunks of 32 keys each (12 x 32 = 384)
+constexpr int kPfParts = 3;                // column parts of the softmax (warps per TMEM lane quadrant)
+constexpr int kPfCpp = 12 / kPfParts;      // 32-key chunks per part (12 x 32 = 384 >= 336 padded keys)
+constexpr int kPfThreads = 64 + 128 * kPfParts;  // TMA warp, MMA warp, 4 x kPfParts softmax / epilogue warps
 constexpr int kPfKeys = 336;               // padded key count (3 MMAs of N = 112)
 constexpr int kPfKeyBlocks = 6;            // 64-key blocks of the P.V product (384 >= 336)
 constexpr uint32_t kPfQBytes = 128 * 64 * 2;
@@ -54,6 +55,17 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const float* v) {
         "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
       : "memory");
 }
+// 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // bit j = pad[key0 + j] != 0 for the 32 keys of chunk c (keys >= P read as 0); P % 8 == 0 and 8-byte aligned rows
 __device__ __forceinline__ uint32_t chunk_mask(const uint8_t* padb, int c, int P) {
@@ -72,7 +84,7 @@ __device__ __forceinline__ uint32_t chunk_mask(const uint8_t* padb, int c, int P
   }
   return m;
 }
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 384;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(128 * kPfParts) : "memory"); }
 
 #ifdef PI0_TIMELINE
 __device__ unsigned long long g_pf_tl[16];
@@ -88,7 +100,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ring = smem;                                          // kPfStages x (Q block | K block)  /  V^T blocks
   uint8_t* ptile = smem + kPfStages * kPfStageBytes;             // 6 x [128 rows x 64 keys], SW128 K-major
-  float* red = reinterpret_cast<float*>(ptile + kPfPBytes);      // [3 parts][128 rows] row max, then row sum
+  float* red = reinterpret_cast<float*>(ptile + kPfPBytes);      // [kPfParts][128 rows] row max, then row sum
+  uint32_t* maskw = reinterpret_cast<uint32_t*>(ptile + kPfPBytes + 1536);   // [12] visibility bits per 32-key chunk
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(ptile + kPfPBytes + 2048);
   uint64_t* empty_bar = full_bar + kPfStages;
   uint64_t* s_full = empty_bar + kPfStages;    // S accumulated            (MMA -> softmax warps)
@@ -201,54 +214,63 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int r = quad * 32 + lane;                       // row of the tile = TMEM lane
     const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
     const float kNeg = -2.3819763e38f;
-    uint8_t* stage2 = ptile + (warp - 2) * 2 * 2048;      // output staging (P tile is dead by then): 12 x 4 KiB
+    uint8_t* stage2 = ptile + (warp - 2) * 2 * 2048;      // output staging (P tile is dead by then): 4 KiB per warp
     uint32_t tile_par = 0;
     for (int idx = blockIdx.x; idx < p.total_tiles; idx += gridDim.x) {
       const int b = idx / p.tiles_per_b, mt = idx - b * p.tiles_per_b;
       const uint8_t* padb = p.pad + (int64_t)b * p.P;
       PF_STAMP(0);
+      // key-visibility bits of the sample, one word per 32-key chunk, fetched while the S MMAs are still running
+      // (the previous tile's readers are past their last use: they all arrived on o_empty's predecessor barriers)
+      if (threadIdx.x - 64 < 12) maskw[threadIdx.x - 64] = chunk_mask(padb, (int)threadIdx.x - 64, p.P);
+      epi_bar();
       mbar_wait(s_full, tile_par);
       tc_fence_after();
       PF_STAMP(1);
       // ---- pass 1 (the only TMEM pass): masked scaled scores of this part's 4 chunks, kept as packed bf16 (they ARE
       //      bf16 values: the reference materialises the scores in bf16), and the row max ----
-      uint32_t sp[4][16];
+      uint32_t sp[kPfCpp][16];
       float mx = -INFINITY;
 #pragma unroll
-      for (int ci = 0; ci < 4; ++ci) {
-        const int c = part * 4 + ci;                     // chunk 11 lies beyond the padded keys: all -inf
-        float v[32];
-        uint32_t msk = 0;
-        if (c < 11) {
-          tmem_ld_32x32(trow + c * 32, v);
-          msk = chunk_mask(padb, c, p.P);
-          tmem_ld_wait();
-        } else {
+      for (int ci = 0; ci < kPfCpp; ++ci) {
+        const int c = part * kPfCpp + ci;                // chunk 11 lies beyond the padded keys: all -inf
+        const uint32_t msk = maskw[c];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0.0f;
-        }
+        for (int hh = 0; hh < 2; ++hh) {
+          float v[16];
+          if (c < 11) {
+            tmem_ld_32x16(trow + c * 32 + hh * 16, v);
+            tmem_ld_wait();
+          } else {
 #pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          const int key = c * 32 + j;
-          float s0 = bf16_round(bf16_round(v[j]) * p.scale), s1 = bf16_round(bf16_round(v[j + 1]) * p.scale);
-          s0 = key < p.P ? (((msk >> j) & 1u) ? s0 : kNeg) : -INFINITY;
-          s1 = key + 1 < p.P ? (((msk >> (j + 1)) & 1u) ? s1 : kNeg) : -INFINITY;
-          const uint32_t w = bf16x2_bits(s1, s0);
-          sp[ci][j >> 1] = w;
-          // the max is taken over what later passes read back (kNeg is not a bf16 value: it rounds here, for all keys alike)
-          mx = fmaxf(mx, fmaxf(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)));
+            for (int j = 0; j < 16; ++j) v[j] = 0.0f;
+          }
+#pragma unroll
+          for (int j = 0; j < 16; j += 2) {
+            const int jj = hh * 16 + j, key = c * 32 + jj;
+            // scale = 2^-4: rnd(acc) * scale is exact in bf16, the reference's second rounding changes nothing
+            float s0 = bf16_round(v[j]) * p.scale, s1 = bf16_round(v[j + 1]) * p.scale;
+            s0 = key < p.P ? (((msk >> jj) & 1u) ? s0 : kNeg) : -INFINITY;
+            s1 = key + 1 < p.P ? (((msk >> (jj + 1)) & 1u) ? s1 : kNeg) : -INFINITY;
+            const uint32_t w = bf16x2_bits(s1, s0);
+            sp[ci][jj >> 1] = w;
+            // the max is taken over what later passes read back (kNeg is not a bf16 value: it rounds here, for all keys alike)
+            mx = fmaxf(mx, fmaxf(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)));
+          }
         }
       }
       PF_STAMP(2);
       red[part * 128 + r] = mx;
       epi_bar();
-      mx = fmaxf(fmaxf(red[r], red[128 + r]), red[256 + r]);
+      mx = red[r];
+#pragma unroll
+      for (int q = 1; q < kPfParts; ++q) mx = fmaxf(mx, red[q * 128 + r]);
       epi_bar();
       // ---- pass 2: row sum of exp(s - max) (ex2.approx: relative error 2^-22, far below the bf16 rounding of p) ----
       const float kLog2e = 1.4426950408889634f;
       float sum = 0.0f;
 #pragma unroll
-      for (int ci = 0; ci < 4; ++ci) {
+      for (int ci = 0; ci < kPfCpp; ++ci) {
 #pragma unroll
         for (int jj = 0; jj < 16; ++jj) {
           const uint32_t w = sp[ci][jj];
@@ -258,12 +280,14 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       PF_STAMP(3);
       red[part * 128 + r] = sum;
       epi_bar();
-      sum = red[r] + red[128 + r] + red[256 + r];
+      sum = red[r];
+#pragma unroll
+      for (int q = 1; q < kPfParts; ++q) sum += red[q * 128 + r];
       const float lsum = __log2f(sum);
       // ---- pass 3: p = rnd(exp(s - max) / sum) = rnd(2^((s - max) log2e - log2 sum)) -> swizzled K-major P tile ----
 #pragma unroll
-      for (int ci = 0; ci < 4; ++ci) {
-        const int c = part * 4 + ci;
+      for (int ci = 0; ci < kPfCpp; ++ci) {
+        const int c = part * kPfCpp + ci;
         uint8_t* blk = ptile + (c >> 1) * (128 * 128) + r * 128;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -290,7 +314,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       PF_STAMP(5);
       int sbuf = 0;
 #pragma unroll 1
-      for (int c = part * 3; c < min(8, part * 3 + 3); ++c) {   // 8 chunks of 32 dims: 3 + 3 + 2
+      constexpr int kOPer = (8 + kPfParts - 1) / kPfParts;   // 8 chunks of 32 dims: 3 + 3 + 2
+      for (int c = part * kOPer; c < min(8, (part + 1) * kOPer); ++c) {
         float v[32];
         tmem_ld_32x32(trow + c * 32, v);
         tmem_ld_wait();
