@@ -67,6 +67,7 @@ struct pi0_ctx {
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
+  int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
   Buf bufs[40];
   int nbufs;
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
@@ -303,7 +304,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
                                c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
   } else if (!suffix && c->prefill_fused && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 &&
              prefill_attention_supported(T, c->P) &&
-             (int64_t)B * ((T * kHeads + 127) / 128) >= 2 * (c->cfg.num_sms > 0 ? c->cfg.num_sms : 148)) {
+             (int64_t)B * ((T * kHeads + 127) / 128) >= c->prefill_fused_min_tiles) {
     // prefix pass, bf16, rollout batches (>= 2 waves of 128-row tiles): scores + masked softmax + P.V of a layer in one
     // tcgen05 launch. A tile is a serial S -> softmax -> P.V chain of ~19 us, so with fewer tiles than SMs (batch 1: 21
     // tiles) the three-launch GEMM chain, which spreads the same work over every SM, is faster (2.30 vs 2.55 ms prefill)
@@ -404,6 +405,8 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
     c->siglip_fused = !(f && strcmp(f, "0") == 0);
     const char* pf = getenv("PI0_PREFILL_FUSED");
     c->prefill_fused = !(pf && strcmp(pf, "0") == 0);
+    const char* pm = getenv("PI0_PREFILL_FUSED_MIN_TILES");
+    c->prefill_fused_min_tiles = pm ? atoi(pm) : 2 * (cfg->num_sms > 0 ? cfg->num_sms : 148);
   }
   const char* mega_env = getenv("PI0_MEGA");
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
