@@ -61,6 +61,23 @@ def bytes_per_chunk_b1(n_cams, lang_len, horizon, num_steps=10):
     return 2 * (414.4e6 + 1981.8e6) + num_steps * (2 * 311.4e6 + kv) + kv
 
 
+def roofline_ms_b1(n_cams, lang_len, horizon, peaks, num_steps=10):
+    """north_star's batch-1 bound, per phase: the slower of FLOPs at the tensor peak and weight + KV bytes at HBM
+    bandwidth (the prefill of a 328-token prefix is 328 FLOP per weight byte: above the ~215 FLOP/B ridge, tensor-bound;
+    SigLIP at 256 tokens sits on the ridge; the 5-row denoise steps are pure weight streaming)."""
+    P, S = n_cams * 256 + lang_len, 1 + horizon
+    kv = 2 * 18 * P * 256 * 2
+    f_sig = n_cams * (2 * 256 * (27 * 15_224_832 + 677_376 + 2_359_296) + 27 * 4 * 256 ** 2 * 1152)
+    f_gem = 2 * 1_981_808_640 * P + 147_456 * P * P
+    f_exp = num_steps * (2 * 311_427_072 * S + 147_456 * S * (P + S))
+    b_sig, b_gem, b_exp = 2 * 414.4e6, 2 * 1981.8e6 + kv, num_steps * (2 * 311.4e6 + kv)
+    tf, bw = peaks["bf16_tflops"] * 1e12, peaks["hbm_gbs"] * 1e9   # burst figures: a 9 ms pass is not power-capped
+    phases = {"siglip": (f_sig, b_sig), "prefill": (f_gem, b_gem), "denoise": (f_exp, b_exp)}
+    out = {k: {"tensor_ms": 1e3 * f / tf, "hbm_ms": 1e3 * b / bw} for k, (f, b) in phases.items()}
+    total = sum(max(v["tensor_ms"], v["hbm_ms"]) for v in out.values())
+    return total, out
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -433,6 +450,11 @@ def b200_arm(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "achieved": by / (p50 * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": by / (p50 * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes": by,
                          "peak_source": peaks["source"]}}
+        rl_ms, rl_ph = roofline_ms_b1(n_cams, lang_len, horizon, peaks)
+        line["latency_b1"]["roofline_per_phase"] = {
+            "bound": "per phase, the slower of FLOPs at the burst bf16 peak and weight + KV bytes at the copy bandwidth",
+            "roofline_ms": rl_ms, "frac": rl_ms / p50, "phases": {k: {a: round(b, 4) for a, b in v.items()}
+                                                                 for k, v in rl_ph.items()}}
 
         # ---- (5) CPU baseline on the host cores (N=1 only) --------------------------------------------------------
         if world == 1 and not args.no_cpu_baseline:
