@@ -8,11 +8,10 @@ for B in 64 1; do
   ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:pi0 -s $N -c $N --csv \
       --log-file gpurun_out/r01c_launches_b$B.csv python tools/profile_step.py $B 2 > gpurun_out/ncu_l$B.log 2>&1
 done
-# full captures: dominant kernel of the batch-64 step (prefill gate/up GeGLU GEMM, CTA-pair kernel) and one short-K
-# SigLIP GEMM of the single-CTA kernel (fc1: 4th <256, store> launch of the pass) for the epilogue analysis
+# full capture: dominant kernel of the batch-64 step (prefill gate/up GeGLU GEMM, CTA-pair kernel). (An earlier version of
+# this script also captured SigLIP fc1 on the single-CTA kernel for the epilogue analysis; those GEMMs now run on the
+# pair kernel with the TMA-store epilogue.)
 ncu --set full --clock-control none --import-source on --kernel-name-base mangled -k regex:gemm_tc_pair_kernelILi256ELi1E -s 2 -c 1 \
     -o gpurun_out/r01c_gateup_pair_b64 python tools/profile_step.py 64 1 > gpurun_out/ncu_f64.log 2>&1
-ncu --set full --clock-control none --import-source on --kernel-name-base mangled -k regex:gemm_tc_kernelILi256ELi0E -s 3 -c 1 \
-    -o gpurun_out/r01c_siglip_fc1_b64 python tools/profile_step.py 64 1 > gpurun_out/ncu_fc1.log 2>&1
-tail -2 gpurun_out/plain64.log gpurun_out/plain1.log gpurun_out/ncu_l64.log gpurun_out/ncu_f64.log gpurun_out/ncu_fc1.log
+tail -2 gpurun_out/plain64.log gpurun_out/plain1.log gpurun_out/ncu_l64.log gpurun_out/ncu_f64.log
 ls -la gpurun_out | tail -12
