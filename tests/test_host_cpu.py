@@ -121,3 +121,28 @@ def test_policy_fails_loudly_without_cuda():
              "task": ["pick"]}
     with pytest.raises(pb.Pi0Error):
         pol.select_action(batch)
+
+
+def test_bench_batch1_roofline_per_phase():
+    """bench.py's batch-1 bound: per phase the slower of tensor time and HBM time; the 328-token prefill is tensor-bound,
+    the 5-row denoise steps are weight streaming, and the FLOP split adds up to flops_per_chunk."""
+    import importlib.util
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(root, "bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    argv, sys.argv = sys.argv, ["bench.py"]
+    try:
+        spec.loader.exec_module(mod)
+    finally:
+        sys.argv = argv
+    peaks = {"bf16_tflops": 1600.0, "hbm_gbs": 6500.0}
+    total, ph = mod.roofline_ms_b1(1, 72, 4, peaks)
+    assert ph["prefill"]["tensor_ms"] > ph["prefill"]["hbm_ms"]
+    assert ph["denoise"]["hbm_ms"] > 10 * ph["denoise"]["tensor_ms"]
+    assert abs(total - sum(max(v.values()) for v in ph.values())) < 1e-9
+    flops = sum(v["tensor_ms"] for v in ph.values()) * 1e-3 * peaks["bf16_tflops"] * 1e12
+    assert abs(flops - mod.flops_per_chunk(1, 72, 4)) <= 1e-6 * flops
+    by = sum(v["hbm_ms"] for v in ph.values()) * 1e-3 * peaks["hbm_gbs"] * 1e9
+    assert abs(by - mod.bytes_per_chunk_b1(1, 72, 4)) <= 1e-6 * by
