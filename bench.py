@@ -196,6 +196,88 @@ def time_cpu_oracle(workload, n_chunks, warmup, log=None):
     return times, cores
 
 
+def time_gpu_eager(workload, B, dev, steps=3, b1_iters=20, log=None):
+    """The reference-equivalent GPU number (BASELINE.md section 2 "GPU-eager"): the same op sequence the
+    reference executes - PyTorch eager, torch.autocast(bfloat16), eager attention, one cuBLAS call per projection, the
+    Python Euler loop - on this B200, same random-init weights / observation shapes / noise as the B200 arm
+    (oracle/pi0_eager.py; the lerobot module itself is not in the tree). Device-timed with CUDA events."""
+    from int_act_b200.weights import Dims, random_state_dict
+    from oracle.pi0_eager import Pi0Eager
+    from oracle.pi0_oracle import OracleDims
+
+    n_cams, lang_len, horizon = WORKLOADS[workload]
+    dims = Dims()
+    sd = random_state_dict(dims, device=dev, seed=0)
+    model = Pi0Eager(OracleDims(n_cams=n_cams, lang_len=lang_len, horizon=horizon), sd, dev, use_bf16=True)
+    del sd
+    torch.cuda.empty_cache()
+
+    def inputs(b, seed):
+        obs = synthetic_observations(b, n_cams, lang_len, seed=seed, pinned=False)
+        imgs = [obs[k].to(dev) for k in obs if k.startswith("observation.images")]
+        masks = [torch.ones(b, dtype=torch.bool, device=dev) for _ in imgs]
+        noise = torch.normal(0.0, 1.0, (b, horizon, 32), generator=torch.Generator().manual_seed(42)).to(dev)
+        return imgs, masks, obs["lang_tokens"].to(dev), obs["lang_masks"].to(dev), obs["observation.state"].to(dev), noise
+
+    out = {}
+    args_b = inputs(B, 1234)
+    model.sample_actions(*args_b)  # warm-up (cuBLAS / cuDNN heuristics, allocator)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        x = model.sample_actions(*args_b)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    assert torch.isfinite(x).all()
+    out.update({"value": B / (ms * 1e-3), "unit": "chunks/s", "ms_per_step": ms, "batch": B, "steps": steps})
+    if log:
+        log(f"gpu eager batch {B}: {ms:.1f} ms/step")
+    args_1 = inputs(1, 1234)
+    lat = []
+    for i in range(3 + b1_iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        model.sample_actions(*args_1)
+        b.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            lat.append(a.elapsed_time(b))
+    lat.sort()
+    out.update({"p50_b1_ms": lat[len(lat) // 2], "p99_b1_ms": lat[-1], "b1_iters": len(lat),
+                "what": "PyTorch eager + torch.autocast(bf16) restatement of the reference's op sequence on this GPU "
+                        "(cuBLAS / cuDNN, eager attention, Python Euler loop), inputs resident in HBM; torch "
+                        f"{torch.__version__}"})
+    del model
+    torch.cuda.empty_cache()
+    return out
+
+
+def eager_arm(args, rank, local_rank):
+    """`--impl eager`: the GPU-eager baseline as its own JSON line (rank 0 only; replicas would time the same thing)."""
+    if rank != 0:
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl eager needs a CUDA device")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    n_cams, lang_len, horizon = WORKLOADS[args.workload]
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    r = time_gpu_eager(args.workload, args.batch, dev, steps=max(1, args.steps), b1_iters=min(args.latency_iters, 30),
+                       log=lambda s: print(s, file=sys.stderr))
+    clocks = sampler.result()
+    emit({"impl": "eager", "metric": "pi0_action_chunks_per_sec", "value": r["value"], "unit": "chunks/s", "n_gpus": 1,
+          "steps": r["steps"], "warmup": 1, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+          "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+          "config": {"workload": f"pi0-{args.workload} infer_action, batch {args.batch}, PyTorch eager + autocast(bf16) on "
+                                 "one B200 (reference-equivalent GPU baseline)", "n_cams": n_cams,
+                     "prefix_tokens": n_cams * 256 + lang_len, "horizon": horizon, "num_steps": 10},
+          "latency_b1": {"p50_ms": r["p50_b1_ms"], "p99_ms": r["p99_b1_ms"], "iters": r["b1_iters"]},
+          "gpu_launches": 0, "clocks": clocks, "what": r["what"]})
+
+
 def reference_arm(args, rank):
     """`--impl reference`: the reference's CPU implementation of the path on the host cores. The reference's own code
     (lerobot PI0Policy) is not in the tree, so this is the oracle port ("kind": "port")."""
@@ -456,10 +538,17 @@ def b200_arm(args, rank, world, local_rank):
             "roofline_ms": rl_ms, "frac": rl_ms / p50, "phases": {k: {a: round(b, 4) for a, b in v.items()}
                                                                  for k, v in rl_ph.items()}}
 
+        # ---- (4b) the reference-equivalent GPU number: PyTorch eager + autocast(bf16) on this same B200 -------------------
+        del policy, eng, st, st1
+        torch.cuda.empty_cache()
+        if not args.no_gpu_eager:
+            ge = time_gpu_eager(args.workload, B, dev, steps=3, b1_iters=20)
+            ge["speedup_batch"] = value / world / ge["value"]
+            ge["speedup_b1_latency"] = ge["p50_b1_ms"] / p50
+            line["gpu_eager"] = ge
+
         # ---- (5) CPU baseline on the host cores (N=1 only) --------------------------------------------------------
         if world == 1 and not args.no_cpu_baseline:
-            del policy, eng
-            torch.cuda.empty_cache()
             times, cores = time_cpu_oracle(args.workload, 2, 1)
             v = len(times) / sum(times)
             line["cpu_baseline"] = {"value": v, "unit": "chunks/s", "cores": cores, "kind": "port",
@@ -476,11 +565,12 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "eager"])
     ap.add_argument("--batch", type=int, default=64, help="observations per GPU per step")
     ap.add_argument("--workload", default="bridge", choices=sorted(WORKLOADS))
     ap.add_argument("--latency-iters", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-eager", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -490,6 +580,8 @@ def main():
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     if args.impl == "reference":
         reference_arm(args, rank)
+    elif args.impl == "eager":
+        eager_arm(args, rank, local_rank)
     else:
         b200_arm(args, rank, world, local_rank)
 

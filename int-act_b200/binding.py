@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpi0b200.so")
+LIB_PATH = os.environ.get("PI0_LIB") or os.path.join(_HERE, "libpi0b200.so")  # PI0_LIB: instrumented dev builds
 
 SIGLIP_LAYERS = 27
 GEMMA_LAYERS = 18

@@ -34,15 +34,22 @@ def _digest():
     return h.hexdigest()
 
 
-def build(force=False, verbose=False):
-    """Compile every .cu under csrc/ to an object (in parallel) and link libpi0b200.so."""
+def build(force=False, verbose=False, variant=""):
+    """Compile every .cu under csrc/ to an object (in parallel) and link libpi0b200.so. `variant` (with
+    PI0_EXTRA_NVCC_FLAGS) builds an instrumented copy libpi0b200_<variant>.so next to it (development aid, see
+    tools/loop_timeline.py; selected at run time with PI0_LIB)."""
+    global LIB, STAMP
+    bdir = "build" + ("_" + variant if variant else "")
+    if variant:
+        LIB = os.path.join(HERE, f"libpi0b200_{variant}.so")
+        STAMP = os.path.join(HERE, bdir, "stamp.txt")
     dig = _digest()
     if not force and os.path.exists(LIB) and os.path.exists(STAMP) and open(STAMP).read().strip() == dig:
         return LIB
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    os.makedirs(os.path.join(HERE, bdir), exist_ok=True)
     procs, objs = [], []
     for src in _sources():
-        obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(HERE, bdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
         cmd = [NVCC] + FLAGS + ["-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -53,7 +60,7 @@ def build(force=False, verbose=False):
         if p.returncode != 0:
             sys.stderr.write(out)
             raise RuntimeError(f"nvcc failed on {src}")
-    with open(os.path.join(HERE, "build", "ptxas.log"), "w") as f:
+    with open(os.path.join(HERE, bdir, "ptxas.log"), "w") as f:
         f.write("\n".join(log))
     if verbose:
         print("\n".join(log))
@@ -64,4 +71,5 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    _variant = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--variant=")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=_variant[0] if _variant else ""))

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "../../include/pi0b200.h"
+#include "denoise_loop.cuh"
 #include "denoise_mega.cuh"
 #include "elementwise.cuh"
 
@@ -64,11 +65,17 @@ struct pi0_ctx {
   unsigned* mega_sync;
   void* mega_sc;
   int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
+  // whole-loop persistent denoise kernel (denoise_loop.cu): unit table, flag-in-data exchange arena and its epoch word
+  int16_t* loop_units;
+  uint4* loop_ll;
+  unsigned* loop_epoch;
+  int loop_pace_ns;  // PI0_LOOP_PACE (development knob)
+  int loop_mode;  // 0 = off, 1 = per-step layers-only launches (PI0_MEGA=2), 2 = the whole Euler loop in one launch (default)
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
   int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
-  Buf bufs[40];
+  Buf bufs[48];
   int nbufs;
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
   bool prof_on;
@@ -100,7 +107,7 @@ struct Carver {
   void* take(const char* name, size_t bytes) {
     size_t o = off;
     off = round_up((int64_t)(off + bytes), 1024);
-    if (ctx && ctx->nbufs < 40) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
+    if (ctx && ctx->nbufs < 48) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
     return base ? base + o : nullptr;
   }
 };
@@ -168,6 +175,9 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.mega_units = (int16_t*)cv.take("mega.units", (size_t)1024 * 4 * (kMegaMaxUnits + 1) * 2);
   x.mega_sync = (unsigned*)cv.take("mega.sync", 64);
   x.mega_sc = cv.take("mega.scores", (size_t)16 * 8 * 640 * 2);
+  x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
+  x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
+  x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
   if (c) {
     c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
     c->kv_pitch = kvp; c->sc_pitch = scp; c->vt_pitch = vtp; c->es = (int)es;
@@ -408,14 +418,28 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
     const char* pm = getenv("PI0_PREFILL_FUSED_MIN_TILES");
     c->prefill_fused_min_tiles = pm ? atoi(pm) : 2 * (cfg->num_sms > 0 ? cfg->num_sms : 148);
   }
+  // PI0_MEGA: 0 = per-op launches, unset / 1 = per-step persistent kernel (grid barriers, denoise_mega.cu), 2 = flag-in-data
+  // kernel launched per step (layers only), 3 = the whole Euler loop in one flag-in-data launch (denoise_loop.cu; measured
+  // slower than 1 so far - 41 vs 28 us per layer - see DESIGN.md 4.2b, so it is opt-in)
   const char* mega_env = getenv("PI0_MEGA");
+  const int mega_sel = mega_env ? atoi(mega_env) : 1;
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
-  if (cfg->dtype == 0 && cfg->gemm_impl == 0 && !(mega_env && strcmp(mega_env, "0") == 0) && sms >= 64 && sms <= 1024) {
+  c->loop_mode = 0;
+  c->loop_pace_ns = getenv("PI0_LOOP_PACE") ? atoi(getenv("PI0_LOOP_PACE")) : 0;
+  if (cfg->dtype == 0 && cfg->gemm_impl == 0 && mega_sel != 0 && sms >= 64 && sms <= 1024) {
     std::vector<int16_t> tab;
     if (mega_build_units(sms, tab) == 0 &&
         cudaMemcpy(c->mega_units, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice) == cudaSuccess &&
         cudaMemset(c->mega_sync, 0, 64) == cudaSuccess) {
       c->mega_ctas = sms;
+    } else {
+      cudaGetLastError();
+    }
+    if (mega_sel >= 2 && sms >= 128 && sms <= 512 && loop_build_units(sms, tab) == 0 &&
+        tab.size() * sizeof(int16_t) <= loop_units_bytes() &&
+        cudaMemcpy(c->loop_units, tab.data(), tab.size() * sizeof(int16_t), cudaMemcpyHostToDevice) == cudaSuccess &&
+        cudaMemset(c->loop_ll, 0, loop_ll_bytes()) == cudaSuccess && cudaMemset(c->loop_epoch, 0, 64) == cudaSuccess) {
+      c->loop_mode = mega_sel == 2 ? 1 : 2;
     } else {
       cudaGetLastError();
     }
@@ -627,6 +651,43 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
   const pi0_weights& w = c->w;
   const float dt = -1.0f / (float)c->cfg.num_steps;
 
+  const bool use_loop = c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(B * S, S, c->P, c->mega_ctas);
+  auto fill_loop = [&](LoopParams& lp) {
+    for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
+      const pi0_gemma_layer_w& lw = w.exp[l];
+      lp.L[l] = MegaLayerW{(const bf16*)lw.wqkv, (const bf16*)lw.wo, (const bf16*)lw.wgu, (const bf16*)lw.wdown, lw.g1,
+                           lw.g2};
+    }
+    lp.n_layers = c->cfg.n_gemma_layers;
+    lp.M = B * S; lp.S = S; lp.P = c->P; lp.B = B; lp.H = H;
+    lp.state_w = (const bf16*)w.state_w; lp.action_in_w = (const bf16*)w.action_in_w;
+    lp.time_in_wa = (const bf16*)w.time_in_wa; lp.time_out_w = (const bf16*)w.time_out_w;
+    lp.action_out_w = (const bf16*)w.action_out_w;
+    lp.state_b = w.state_b; lp.action_in_b = w.action_in_b; lp.time_bias = w.time_bias; lp.time_out_b = w.time_out_b;
+    lp.action_out_b = w.action_out_b; lp.exp_norm_g = w.exp_norm_g;
+    lp.state = state; lp.x_t = x_t; lp.dt = dt;
+    lp.x0 = (const bf16*)c->suf; lp.x = (bf16*)c->xe;
+    lp.kcache = (bf16*)c->kcache; lp.vtcache = (bf16*)c->vtcache;
+    lp.kc_layer_stride = (int64_t)c->maxB * c->kv_pitch * kHd;
+    lp.vt_layer_stride = (int64_t)c->maxB * kHd * c->vt_pitch;
+    lp.kv_pitch = c->kv_pitch; lp.vt_pitch = c->vt_pitch;
+    lp.rope_cos = w.rope_cos; lp.rope_sin = w.rope_sin; lp.pos_ids = c->suffix_pos; lp.pad = c->pad;
+    lp.cum = c->suffix_cum; lp.units = c->loop_units; lp.ll = c->loop_ll; lp.epoch = c->loop_epoch;
+    lp.kp = (c->P + S + 31) / 32 * 32;
+    lp.pace_ns = c->loop_pace_ns;
+  };
+  const int n_iters = c->cfg.n_euler_iters > 0 ? c->cfg.n_euler_iters : c->cfg.num_steps;
+  if (use_loop && c->loop_mode == 2) {
+    // latency regime: embed_suffix, the 18 expert layers, the action head and the Euler update of ALL steps in one
+    // persistent cooperative launch (denoise_loop.cu)
+    PROF("denoise.loop_mega");
+    LoopParams lp = {};
+    fill_loop(lp);
+    lp.n_steps = n_iters;
+    lp.layers_only = 0;
+    return loop_denoise(lp, c->mega_ctas, s);
+  }
+
   // state_proj -> suffix row 0 of every sample (input-independent across steps)
   PI0_TRY(run_cast(c, "denoise.cast", state, c->st_act, (int64_t)B * 32, s));
   {
@@ -636,7 +697,6 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
     g.epi.rpb_in = 1; g.epi.rpb_out = S; g.epi.row_off = 0;
     PI0_TRY(run_gemm(c, "denoise.state_proj", g, s));
   }
-  const int n_iters = c->cfg.n_euler_iters > 0 ? c->cfg.n_euler_iters : c->cfg.num_steps;
   for (int step = 0; step < n_iters; ++step) {
     // embed_suffix: action_in_proj -> (time half folded into the bias) mlp_in -> SiLU -> mlp_out -> suffix rows 1..H
     PI0_TRY(run_cast(c, "denoise.cast", x_t, c->xt_act, (int64_t)B * H * 32, s));
@@ -660,7 +720,15 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
       g.epi.rpb_in = H; g.epi.rpb_out = S; g.epi.row_off = 1;
       PI0_TRY(run_gemm(c, "denoise.time_mlp_out", g, s));
     }
-    if (c->mega_ctas > 0 && mega_supported(B * S, S, c->P)) {
+    if (use_loop) {
+      // PI0_MEGA=2: the flag-in-data kernel as a per-step drop-in for the round-1 kernel (A/B tests)
+      PROF("denoise.layers_mega");
+      LoopParams lp = {};
+      fill_loop(lp);
+      lp.n_steps = 1;
+      lp.layers_only = 1;
+      PI0_TRY(loop_denoise(lp, c->mega_ctas, s));
+    } else if (c->mega_ctas > 0 && mega_supported(B * S, S, c->P)) {
       // latency regime: all expert layers of this step in one persistent cooperative launch
       PROF("denoise.layers_mega");
       MegaParams mp = {};
