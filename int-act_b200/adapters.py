@@ -90,6 +90,17 @@ def _cfg_get(config, path: Sequence[str], default=None):
     return default if cur is None else cur
 
 
+def _on_device(fn):
+    """Runs an adapter method with the adapter's device current (the calling thread may sit on another GPU)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(self, *a, **kw):
+        with torch.cuda.device(self.device):
+            return fn(self, *a, **kw)
+    return wrapped
+
+
 class _GpuAdapterBase:
     """Shared state: statistics on the device (float64), resize tables per input size, the C-ABI handle."""
 
@@ -132,6 +143,7 @@ class _GpuAdapterBase:
             self._tables[key] = (torch.from_numpy(idx).to(self.device), torch.from_numpy(w).to(self.device), prec)
         return self._tables[key]
 
+    @_on_device
     def resize_normalize(self, images_u8: torch.Tensor) -> torch.Tensor:
         """uint8 [B, H, W, 3] on the device -> float32 [B, 3, h, w] in [-1, 1] (simplerMS3.py:50-63)."""
         B, H, W, C = images_u8.shape
@@ -144,9 +156,10 @@ class _GpuAdapterBase:
         images_u8 = images_u8.contiguous()
         pb.check(self.lib.pi0_adapter_resize_normalize(pb.ptr(images_u8), pb.ptr(out), B, H, W, oh, ow, pb.ptr(xi),
                                                        pb.ptr(xw), xp, pb.ptr(yi), pb.ptr(yw), yp, 1.0 / 255.0, 0.5, 0.5,
-                                                       pb.current_stream()), "pi0_adapter_resize_normalize")
+                                                       pb.current_stream(self.device)), "pi0_adapter_resize_normalize")
         return out
 
+    @_on_device
     def lanczos4_normalize(self, images_u8: torch.Tensor) -> torch.Tensor:
         """uint8 [B, H, W, 3] on the device -> float32 [B, 3, h, w] in [-1, 1]: cv2.INTER_LANCZOS4 resize (bit-exact with
         OpenCV's generic uint8 path) + x/255 + (x-0.5)/0.5 (simpler.py:47-65)."""
@@ -164,9 +177,10 @@ class _GpuAdapterBase:
         images_u8 = images_u8.contiguous()
         pb.check(self.lib.pi0_adapter_lanczos4_normalize(pb.ptr(images_u8), pb.ptr(out), B, H, W, oh, ow, pb.ptr(xo),
                                                          pb.ptr(xc), pb.ptr(yo), pb.ptr(yc), 1.0 / 255.0, 0.5, 0.5,
-                                                         pb.current_stream()), "pi0_adapter_lanczos4_normalize")
+                                                         pb.current_stream(self.device)), "pi0_adapter_lanczos4_normalize")
         return out
 
+    @_on_device
     def proprio(self, eef: torch.Tensor) -> torch.Tensor:
         """eef [B, 8] (float32 / float64, device) -> normalised state float32 [B, 7] carrying the rounding of
         `torch.as_tensor(proprio, dtype=self.dtype)` (simplerMS3.py:66-88,153-165)."""
@@ -178,17 +192,18 @@ class _GpuAdapterBase:
         pb.check(self.lib.pi0_adapter_proprio(pb.ptr(eef), int(eef.dtype == torch.float64), pb.ptr(out), B,
                                               pb.ptr(self._pa), pb.ptr(self._pb),
                                               0 if self.state_normalization_type == "bound" else 1,
-                                              int(self.dtype == torch.bfloat16), pb.current_stream()),
+                                              int(self.dtype == torch.bfloat16), pb.current_stream(self.device)),
                  "pi0_adapter_proprio")
         return out
 
+    @_on_device
     def _postprocess_device(self, actions: torch.Tensor) -> torch.Tensor:
         a = actions.to(self.device, torch.float32).contiguous()
         n = a.numel() // 7
         out = torch.empty(a.shape, dtype=torch.float64, device=self.device)
         pb.check(self.lib.pi0_adapter_postprocess(pb.ptr(a), pb.ptr(out), n, pb.ptr(self._aa), pb.ptr(self._ab),
                                                   0 if self.action_normalization_type == "bound" else 1,
-                                                  pb.current_stream()), "pi0_adapter_postprocess")
+                                                  pb.current_stream(self.device)), "pi0_adapter_postprocess")
         return out
 
     def postprocess(self, actions) -> np.ndarray:

@@ -154,9 +154,11 @@ def ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
-def current_stream():
+def current_stream(device=None):
+    """The calling thread's current stream ON `device` (not on the thread's current device: a server worker thread starts
+    on cuda:0 whatever device the engine lives on)."""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
 def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bias=None, res=None, ldr=None,

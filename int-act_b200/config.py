@@ -102,7 +102,18 @@ class PI0Config:
 
     @property
     def n_cams(self) -> int:
-        return len(self.image_features) + int(self.empty_cameras)
+        """Cameras the prefix is built for: every VISUAL input feature, the `empty_camera_<i>` placeholders that
+        validate_features adds included."""
+        return len(self.image_features)
+
+    def validate_features(self) -> None:
+        """lerobot's PI0Config.validate_features: `empty_cameras` placeholder cameras become input features named
+        `observation.images.empty_camera_<i>`; they are never in a batch, so prepare_images fills them with -1 images and
+        a zero mask ([mirror] modeling_mvla.py:375-383). Idempotent (a config.json that already lists them is fine)."""
+        for i in range(int(self.empty_cameras)):
+            key = f"observation.images.empty_camera_{i}"
+            if key not in self.input_features:
+                self.input_features[key] = PolicyFeature(type="VISUAL", shape=(3, 480, 640))
 
     # ---- construction -------------------------------------------------------------------------------------
     @classmethod

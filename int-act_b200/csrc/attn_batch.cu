@@ -315,10 +315,10 @@ int decode_attention_batch(const void* q, const void* kcache, const void* vtcach
   const size_t vbytes = (size_t)256 * vpitch + 64;  // + the tail the last row's final chunk may touch
   const size_t smem = (kq > vbytes ? kq : vbytes) + (size_t)kRows * kSPitch;
   PI0_REQUIRE(vbytes <= kq, "decode_attention_batch: V^T tile (%zu B) exceeds the K|Q region (%zu B)", vbytes, kq);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
+  static PerDeviceOnce smem_once;
+  if (smem_once.need_more(smem)) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(batch_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+    smem_once.raise(smem);
   }
   p.hpg = B * 2 <= 160 ? 4 : 8;  // two CTAs per sample while they still fit one wave
   PI0_CHECK_CUDA(launch_pdl(batch_attn_kernel, dim3(8 / p.hpg, B), dim3(256), smem, s, 1, p));

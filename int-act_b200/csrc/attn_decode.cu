@@ -44,10 +44,10 @@ int decode_attention(const void* q, const void* kcache, const void* vtcache, voi
   while (hpg > 1 && B * (8 / hpg) < num_sms / 2) hpg >>= 1;
   const int sc_pitch = kp + 16;  // fp32 elements; (kp + 16) * 4 B = 64 mod 128
   const size_t smem = attn_smem_bytes(3, sc_pitch);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
+  static PerDeviceOnce smem_once;
+  if (smem_once.need_more(smem)) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(decode_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+    smem_once.raise(smem);
   }
   PI0_CHECK_CUDA(launch_pdl(decode_attn_kernel, dim3(8 / hpg, B), dim3(256), smem, s, 1, (const bf16*)q,
                             (const bf16*)kcache, (const bf16*)vtcache, (bf16*)att, pad, cum, S, P, kv_pitch, vt_pitch,

@@ -368,10 +368,10 @@ int prefill_attention(const void* q, const void* kcache, const void* vtcache, vo
                       int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s) {
   PI0_REQUIRE(q && kcache && vtcache && att && pad && B >= 1, "prefill_attention: bad argument");
   PI0_REQUIRE(prefill_attention_supported(T, P), "prefill_attention: unsupported shape T=%d P=%d", T, P);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPfSmem));
-    attr_set = true;
+    attr_once.mark();
   }
   const int R = T * 8;
   CUtensorMap tmQ, tmK, tmV, tmO;

@@ -162,10 +162,10 @@ __global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restr
 
 int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s) {
   PI0_REQUIRE(qkv && att && B >= 1, "siglip_attention: bad argument");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(siglip_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    attr_set = true;
+    attr_once.mark();
   }
   PI0_CHECK_CUDA(launch_pdl(siglip_attn_kernel, dim3(kT / kQRows, kHeadsS, B), dim3(256), kSmemBytes, s, 1,
                             (const bf16*)qkv, (bf16*)att, 0.11785113019775793f));

@@ -79,6 +79,24 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   return cudaLaunchKernelEx(&lc, kernel, args...);
 }
 
+// cudaFuncSetAttribute is PER DEVICE: a process-wide "already set" flag left every device but the first without the
+// shared-memory opt-in (engines on cuda:1.., or two GPUs in one server process). Keyed by the current device ordinal.
+struct PerDeviceOnce {
+  bool done[64] = {};
+  size_t level[64] = {};
+  int dev = -1;
+  bool need() {
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = -1;
+    return dev < 0 || dev >= 64 || !done[dev];
+  }
+  void mark() { if (dev >= 0 && dev < 64) done[dev] = true; }
+  bool need_more(size_t v) {  // monotone variant: the attribute must cover the largest size seen on this device
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = -1;
+    return dev < 0 || dev >= 64 || v > level[dev];
+  }
+  void raise(size_t v) { if (dev >= 0 && dev < 64) level[dev] = v; }
+};
+
 // ---------------------------------------------------------------------------------------------
 // numeric helpers
 // ---------------------------------------------------------------------------------------------

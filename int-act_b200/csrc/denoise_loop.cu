@@ -1065,15 +1065,13 @@ int loop_denoise(const LoopParams& p, int num_ctas, cudaStream_t s) {
   PI0_REQUIRE(16 * attn_p_pitch_bytes(p.kp) <= (m16 ? LoopCfg<true>::kABytes : LoopCfg<false>::kABytes) &&
                   p.kp <= 32 * kMegaKeyChunks && p.kp % 32 == 0 && p.ll != nullptr && p.epoch != nullptr,
               "denoise loop kernel: attention scratch does not fit");
-  int dev = 0;
-  PI0_CHECK_CUDA(cudaGetDevice(&dev));
-  static bool attr_set[64] = {};
-  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)LoopCfg<true>::kSmem));
     PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)LoopCfg<false>::kSmem));
-    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    attr_once.mark();
   }
   cudaLaunchConfig_t lc = {};
   lc.gridDim = dim3((unsigned)num_ctas);

@@ -457,13 +457,13 @@ int mega_denoise_layers(const MegaParams& p, int num_ctas, cudaStream_t s) {
   PI0_REQUIRE(16 * attn_p_pitch_bytes(p.kp) <= (m16 ? MegaCfg<true>::kABytes : MegaCfg<false>::kABytes) && p.kp <= 32 * kMegaKeyChunks &&
                   p.kp % 32 == 0 && p.sc != nullptr,
               "denoise mega kernel: attention scratch does not fit");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)MegaCfg<true>::kSmem));
     PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)MegaCfg<false>::kSmem));
-    attr_set = true;
+    attr_once.mark();
   }
   cudaLaunchConfig_t lc = {};
   lc.gridDim = dim3((unsigned)num_ctas);

@@ -771,13 +771,13 @@ static int make_out_map(CUtensorMap* map, const GemmProblem& g) {
 template <int BN, int EPI>
 static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_t stream) {
   using Cfg = TcCfg<BN>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytesStaged));
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_splitk_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytes));
-    attr_set = true;
+    attr_once.mark();
   }
   CUtensorMap tmA, tmB;
   // a single short M tile only fetches the rows that exist (rounded to the 8-row swizzle atom): the MMA still reads
@@ -849,11 +849,11 @@ static int max_active_pairs(int num_sms) {
 template <int BN, int EPI>
 static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   using Cfg = Tc2Cfg<BN>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
     PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_pair_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytes));
-    attr_set = true;
+    attr_once.mark();
   }
   CUtensorMap tmA, tmB;
   PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, kBM));

@@ -56,8 +56,11 @@ class Pi0Engine:
             pb.check(-2, "pi0_workspace_bytes")
         self.workspace = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
         self.ctx = C.c_void_p()
-        pb.check(self.lib.pi0_ctx_create(C.byref(cfg), C.byref(packed.struct), pb.ptr(self.workspace), nbytes,
-                                         C.byref(self.ctx)), "pi0_ctx_create")
+        # every call into the library runs with the engine's device current: kernel attributes, cudaMemcpy / cudaMemset of
+        # pi0_ctx_create and the launches themselves all act on the CURRENT device of the calling thread
+        with torch.cuda.device(self.device):
+            pb.check(self.lib.pi0_ctx_create(C.byref(cfg), C.byref(packed.struct), pb.ptr(self.workspace), nbytes,
+                                             C.byref(self.ctx)), "pi0_ctx_create")
         self.use_cuda_graph = use_cuda_graph
         self._graphs: Dict[int, dict] = {}
         self.launches_per_infer: Dict[int, int] = {}
@@ -75,8 +78,10 @@ class Pi0Engine:
                    lang_masks: torch.Tensor, state: torch.Tensor, x_t: torch.Tensor):
         arr = (C.c_void_p * self.n_cams)(*[t.data_ptr() for t in images])
         scale, shift = (1.0, 0.0) if self.images_pre_normalized else (2.0, -1.0)
-        pb.check(self.lib.pi0_infer(self.ctx, B, arr, scale, shift, pb.ptr(img_masks), pb.ptr(tokens),
-                                    pb.ptr(lang_masks), pb.ptr(state), pb.ptr(x_t), pb.current_stream()), "pi0_infer")
+        with torch.cuda.device(self.device):
+            pb.check(self.lib.pi0_infer(self.ctx, B, arr, scale, shift, pb.ptr(img_masks), pb.ptr(tokens),
+                                        pb.ptr(lang_masks), pb.ptr(state), pb.ptr(x_t), pb.current_stream(self.device)),
+                     "pi0_infer")
 
     def _static(self, B: int) -> dict:
         """Static input/output buffers (and, lazily, the captured CUDA graph) for batch size B."""
@@ -96,6 +101,10 @@ class Pi0Engine:
         return st
 
     def _run_static(self, B: int):
+        with torch.cuda.device(self.device):
+            self._run_static_on_device(B)
+
+    def _run_static_on_device(self, B: int):
         st = self._static(B)
         if not self.use_cuda_graph:
             self._infer_raw(B, st["images"], st["img_masks"], st["tokens"], st["lang_masks"], st["state"], st["x_t"])
@@ -105,10 +114,10 @@ class Pi0Engine:
             # sample_actions launch sequence into one graph: no host work between the ~2k launches at replay
             keep = st["x_t"].clone()
             side = torch.cuda.Stream(device=self.device)
-            side.wait_stream(torch.cuda.current_stream())
+            side.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(side):
                 self._infer_raw(B, st["images"], st["img_masks"], st["tokens"], st["lang_masks"], st["state"], st["x_t"])
-            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.current_stream(self.device).wait_stream(side)
             torch.cuda.synchronize(self.device)
             st["x_t"].copy_(keep)
             g = torch.cuda.CUDAGraph()
@@ -119,6 +128,16 @@ class Pi0Engine:
             st["x_t"].copy_(keep)
             st["graph"] = g
         st["graph"].replay()
+
+    def warm(self, B: int):
+        """Allocates the static buffers of batch size B and captures its CUDA graph on a dummy observation (one valid text
+        token, zero image), so the first real request of that size only replays."""
+        st = self._static(B)
+        if st["graph"] is None:
+            st["tokens"][:, 0] = 2
+            st["lang_masks"][:, 0] = 1
+            self._run_static(B)
+            torch.cuda.synchronize(self.device)
 
     # ---- public: sample_actions -------------------------------------------------------------------------------
     @torch.no_grad()

@@ -25,7 +25,8 @@ import torch.nn.functional as F
 from . import binding as pb
 from .config import PI0Config
 from .engine import Pi0Engine
-from .weights import Dims, PackedWeights, load_safetensors, random_state_dict
+from .weights import (Dims, PackedWeights, canonical_state_dict, load_safetensors, random_state_dict, split_checkpoint,
+                      stats_from_buffers)
 
 OBS_ROBOT = "observation.state"
 ACTION = "action"
@@ -84,6 +85,38 @@ class HFTokenizer:
         return out["input_ids"], out["attention_mask"].bool()
 
 
+# ---- adapt_to_pi_aloha ([mirror] modeling_mvla.py:166-218,409-425): joint flips + gripper linear <-> angular maps ------
+def _aloha_gripper_to_angular(value: torch.Tensor) -> torch.Tensor:
+    value = value * (0.05800 - 0.01844) + 0.01844               # Aloha's linear gripper position
+    horn_radius, arm_length = 0.022, 0.036                      # Interbotix linkage constants
+    value = (horn_radius ** 2 + value ** 2 - arm_length ** 2) / (2 * horn_radius * value)
+    value = torch.arcsin(torch.clamp(value, -1.0, 1.0))
+    return (value - 0.4) / (1.5 - 0.4)                          # measured joint range -> [0, 1]
+
+
+def _aloha_gripper_from_angular(value: torch.Tensor) -> torch.Tensor:
+    value = value * (1.5 - 0.4) + 0.4
+    return (value - (-0.6213)) / (1.4910 - (-0.6213))
+
+
+def pi_aloha_decode_state(state: torch.Tensor) -> torch.Tensor:
+    state = state.clone()
+    for motor_idx in (1, 2, 8, 9):
+        state[:, motor_idx] *= -1
+    for motor_idx in (6, 13):
+        state[:, motor_idx] = _aloha_gripper_to_angular(state[:, motor_idx])
+    return state
+
+
+def pi_aloha_encode_actions(actions: torch.Tensor) -> torch.Tensor:
+    actions = actions.clone()
+    for motor_idx in (1, 2, 8, 9):
+        actions[:, :, motor_idx] *= -1
+    for motor_idx in (6, 13):
+        actions[:, :, motor_idx] = _aloha_gripper_from_angular(actions[:, :, motor_idx])
+    return actions
+
+
 class _Normalizer:
     """lerobot Normalize / Unnormalize restated: IDENTITY, MEAN_STD ((x-mean)/(std+1e-8)), MIN_MAX (to [-1,1])."""
 
@@ -126,7 +159,7 @@ class PI0Policy:
     def __init__(self, config: PI0Config, dataset_stats: Optional[dict] = None, *, state_dict: Optional[dict] = None,
                  dims: Optional[Dims] = None, seed: int = 0, max_batch: int = 1, tokenizer=None,
                  use_cuda_graph: bool = True, device=None):
-        config.validate_features() if hasattr(config, "validate_features") else None
+        config.validate_features()
         self.config = config
         self.normalize_inputs = _Normalizer(config.input_features, config.normalization_mapping, dataset_stats, False)
         self.unnormalize_outputs = _Normalizer(config.output_features, config.normalization_mapping, dataset_stats, True)
@@ -152,8 +185,14 @@ class PI0Policy:
                         **kw) -> "PI0Policy":
         if config is None:
             config = PI0Config.from_pretrained(pretrained_name_or_path)
-        sd = load_safetensors(pretrained_name_or_path, device="cpu")
+        config.validate_features()
+        raw = load_safetensors(pretrained_name_or_path, device="cpu")
+        sd = canonical_state_dict(raw, strict=strict)  # key / shape validation, tied lm_head alias
         stats = kw.pop("dataset_stats", None)
+        if stats is None:
+            # lerobot keeps the dataset statistics inside the checkpoint as Normalize / Unnormalize buffers: the reference
+            # wrapper never passes dataset_stats (policy_wrapper.py:159-162) and MEAN_STD configs (hf_pi0.json:4-8) rely on them
+            stats = stats_from_buffers(split_checkpoint(raw)[1], config.input_features, config.output_features) or None
         return cls(config, stats, state_dict=sd, **kw)
 
     def to(self, arg):
@@ -214,6 +253,16 @@ class PI0Policy:
                                  use_cuda_graph=self._use_cuda_graph)
         return self._engine
 
+    def precapture(self, batch_sizes):
+        """Builds the engine for the largest batch size and captures the CUDA graph of each size now (server start-up),
+        instead of inside the latency of the first request that happens to have that size."""
+        sizes = sorted({int(b) for b in batch_sizes if int(b) >= 1})
+        if not sizes:
+            return
+        eng = self._ensure_engine(sizes[-1])
+        for b in sizes:
+            eng.warm(b)
+
     # ---- preparation ([mirror] modeling_mvla.py:344-407,436-439) ------------------------------------------------------
     def prepare_images(self, batch):
         images, img_masks = [], []
@@ -260,7 +309,8 @@ class PI0Policy:
     def infer_action(self, batch: Dict[str, torch.Tensor], noise: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One action chunk per observation: Tensor[B, n_action_steps, action_dim] (what select_action enqueues)."""
         if self.config.adapt_to_pi_aloha:
-            raise NotImplementedError("adapt_to_pi_aloha is out of scope of the bridge hot path (SURVEY.md section 8f-4)")
+            batch = dict(batch)
+            batch[OBS_ROBOT] = pi_aloha_decode_state(batch[OBS_ROBOT])
         batch = self.normalize_inputs(batch)
         images, img_masks = self.prepare_images(batch)
         state = batch[OBS_ROBOT]
@@ -269,7 +319,10 @@ class PI0Policy:
         actions = eng.sample_actions(images, img_masks, lang_tokens, lang_masks, state, noise)
         original_action_dim = self.config.action_feature.shape[0]
         actions = actions[:, :, :original_action_dim]
-        return self.unnormalize_outputs({ACTION: actions})[ACTION]
+        actions = self.unnormalize_outputs({ACTION: actions})[ACTION]
+        if self.config.adapt_to_pi_aloha:
+            actions = pi_aloha_encode_actions(actions)
+        return actions
 
     @torch.no_grad()
     def select_action(self, batch: Dict[str, torch.Tensor], noise: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -7,21 +7,30 @@ else is an observation -> reply = msgpack(ndarray float64 [action_step, 7] or [B
 Any exception in the handler -> the traceback as a TEXT frame, close code 1011, re-raise; a closed connection ends the
 handler quietly.
 
-What differs from the reference is scheduling, not bytes: the reference runs `select_action` inside the coroutine, so
-the event loop (and every other connection) stalls for the whole inference. Here requests go to one inference worker
-thread through a queue; requests that arrive while the GPU is busy (or within `batch_window_ms`) are coalesced, up to
-`max_batch`, into ONE engine batch (`LeRobotPolicyWrapper.select_action_many`). `max_batch=1` (default) is the
-reference's one-at-a-time behaviour. Control messages act as barriers: they are executed by the same worker, in
-arrival order.
+What differs from the reference is scheduling, not bytes:
+  * the reference runs `select_action` inside the coroutine, so the event loop (and every other connection) stalls for
+    the whole inference. Here requests go through a queue to inference worker threads; requests that arrive while the
+    GPU is busy (or within `batch_window_ms`) are coalesced, up to `max_batch`, into ONE engine batch
+    (`LeRobotPolicyWrapper.select_action_many`). `max_batch=1` (default) is the reference's one-at-a-time behaviour;
+  * the reference scales out with N server processes on N ports (doc/evaluation.md:119-135). `replicas=[wrapper_gpu1,
+    ...]` puts N engines (one per GPU of the box) behind ONE port: every replica has its own worker thread pulling
+    coalesced groups from the shared queue, so the box's GPUs are load-balanced by whoever is free;
+  * control messages are barriers: the queue is drained, every in-flight group finishes, then the message is applied to
+    EVERY replica, in arrival order;
+  * a request that fails (e.g. a malformed observation) only fails its own connection: when a coalesced group raises, its
+    requests are re-run one by one so that only the offender gets the traceback frame, as in the reference.
+`stats` counts requests / batches and keeps the last 4096 request latencies (queue wait + inference); `latency_ms()`
+returns their p50 / p99.
 """
 import asyncio
 import logging
 import threading
 import time
 import traceback
+from collections import deque
 from concurrent.futures import Future
 from queue import Empty, Queue
-from typing import Optional
+from typing import List, Optional
 
 import websockets.asyncio.server
 import websockets.exceptions
@@ -32,7 +41,8 @@ from . import msgpack_numpy
 
 class WebsocketPolicyServer:
     def __init__(self, policy, host: str = "0.0.0.0", port: int = 8000, metadata: Optional[dict] = None, *,
-                 max_batch: int = 1, batch_window_ms: float = 0.0) -> None:
+                 max_batch: int = 1, batch_window_ms: float = 0.0, replicas: Optional[List[object]] = None) -> None:
+        self._policies = [policy] + list(replicas or [])
         self._policy = policy
         self._host, self._port = host, port
         self._metadata = metadata or {}
@@ -41,9 +51,22 @@ class WebsocketPolicyServer:
         self.logger = logging.getLogger("policy_server")
         self.logger.setLevel(logging.INFO)
         self._queue: "Queue[tuple]" = Queue()
-        self._worker: Optional[threading.Thread] = None
+        self._workers: List[threading.Thread] = []
         self._stop = threading.Event()
-        self.stats = {"requests": 0, "batches": 0, "max_batch_seen": 0}
+        self._lock = threading.Condition()
+        self._inflight = 0          # groups being run by some replica
+        self._control_pending = 0   # control messages waiting for the barrier
+        self._lat_ms = deque(maxlen=4096)
+        self.stats = {"requests": 0, "batches": 0, "max_batch_seen": 0, "replicas": len(self._policies),
+                      "per_replica_batches": [0] * len(self._policies), "failed_requests": 0}
+
+    def latency_ms(self) -> dict:
+        """p50 / p99 / max of the last (up to 4096) request latencies: enqueue -> result ready, in milliseconds."""
+        lat = sorted(self._lat_ms)
+        if not lat:
+            return {"n": 0}
+        return {"n": len(lat), "p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(len(lat) * 0.99))],
+                "max": lat[-1]}
 
     # ---- lifecycle ---------------------------------------------------------------------------------------------------
     def serve_forever(self) -> None:
@@ -52,7 +75,7 @@ class WebsocketPolicyServer:
         asyncio.run(self.run())
 
     async def run(self, ready: Optional[asyncio.Event] = None, stop: Optional[asyncio.Event] = None):
-        self._start_worker()
+        self._start_workers()
         try:
             async with websockets.asyncio.server.serve(self._handler, self._host, self._port, compression=None,
                                                        max_size=None) as server:
@@ -64,33 +87,47 @@ class WebsocketPolicyServer:
                 else:
                     await stop.wait()
         finally:
-            self._stop_worker()
+            self._stop_workers()
 
-    def _start_worker(self):
-        if self._worker is None or not self._worker.is_alive():
-            self._stop.clear()
-            self._worker = threading.Thread(target=self._worker_loop, name="pi0-inference", daemon=True)
-            self._worker.start()
+    def _start_workers(self):
+        if any(w.is_alive() for w in self._workers):
+            return
+        self._stop.clear()
+        self._workers = [threading.Thread(target=self._worker_loop, args=(i,), name=f"pi0-inference-{i}", daemon=True)
+                         for i in range(len(self._policies))]
+        for w in self._workers:
+            w.start()
 
-    def _stop_worker(self):
+    def _stop_workers(self):
         self._stop.set()
-        self._queue.put(("stop", None, None))
-        if self._worker is not None:
-            self._worker.join(timeout=5.0)
+        for _ in self._workers:
+            self._queue.put(("stop", None, None, 0.0))
+        for w in self._workers:
+            w.join(timeout=5.0)
 
-    # ---- inference worker: owns the policy, batches what is waiting ---------------------------------------------------
-    def _worker_loop(self):
+    # ---- inference workers: one per replica, each batches what is waiting -----------------------------------------------
+    def _worker_loop(self, idx: int):
+        policy = self._policies[idx]
         pending = None
         while not self._stop.is_set():
-            item = pending if pending is not None else self._queue.get()
-            pending = None
-            kind, payload, fut = item
+            if pending is None:
+                with self._lock:  # a pending control message is a barrier: take no new work until it has run
+                    while self._control_pending and not self._stop.is_set():
+                        self._lock.wait(timeout=0.05)
+                item = self._queue.get()
+            else:
+                item, pending = pending, None
+            kind, payload, fut, t_in = item
             if kind == "stop":
                 break
             if kind != "infer":
-                self._run(fut, lambda: self._control(kind, payload))
+                self._run_control(kind, payload, fut)
                 continue
-            group = [(payload, fut)]
+            with self._lock:  # a control message taken by another worker meanwhile runs first (it is a barrier)
+                while self._control_pending and not self._stop.is_set():
+                    self._lock.wait(timeout=0.05)
+                self._inflight += 1
+            group = [(payload, fut, t_in)]
             deadline = time.monotonic() + self._window_s
             while len(group) < self._max_batch:
                 try:
@@ -98,43 +135,87 @@ class WebsocketPolicyServer:
                     nxt = self._queue.get_nowait() if timeout <= 0 else self._queue.get(timeout=timeout)
                 except Empty:
                     break
-                if nxt[0] != "infer":  # a control message is a barrier: run the group first, then the message
+                if nxt[0] != "infer":  # a control message / stop is a barrier: run the group first, then the message
                     pending = nxt
+                    if nxt[0] in ("switch", "reset"):
+                        with self._lock:
+                            self._control_pending += 1
                     break
-                group.append((nxt[1], nxt[2]))
-            self.stats["requests"] += len(group)
-            self.stats["batches"] += 1
-            self.stats["max_batch_seen"] = max(self.stats["max_batch_seen"], len(group))
+                group.append((nxt[1], nxt[2], nxt[3]))
+            with self._lock:
+                self.stats["requests"] += len(group)
+                self.stats["batches"] += 1
+                self.stats["per_replica_batches"][idx] += 1
+                self.stats["max_batch_seen"] = max(self.stats["max_batch_seen"], len(group))
             try:
-                if len(group) == 1 or not hasattr(self._policy, "select_action_many"):
-                    results = [self._policy.select_action(o) for o, _ in group]
-                else:
-                    results = self._policy.select_action_many([o for o, _ in group])
-                for (_, f), r in zip(group, results):
-                    f.set_result(r)
-            except Exception as e:  # noqa: BLE001 - every waiting request gets the failure
-                for _, f in group:
-                    if not f.done():
-                        f.set_exception(e)
+                self._run_group(policy, group)
+            finally:
+                with self._lock:
+                    self._inflight -= 1
+                    self._lock.notify_all()
+            if pending is not None and pending[0] in ("switch", "reset"):
+                k, pl, f, _ = pending
+                pending = None
+                self._run_control(k, pl, f, counted=True)
+
+    def _finish(self, fut: Future, t_in: float, result=None, exc: Optional[BaseException] = None):
+        self._lat_ms.append(1e3 * (time.monotonic() - t_in))
+        if exc is not None:
+            self.stats["failed_requests"] += 1
+            fut.set_exception(exc)
+        else:
+            fut.set_result(result)
+
+    def _run_group(self, policy, group):
+        try:
+            if len(group) == 1 or not hasattr(policy, "select_action_many"):
+                results = [policy.select_action(o) for o, _, _ in group]
+            else:
+                results = policy.select_action_many([o for o, _, _ in group])
+        except Exception:  # noqa: BLE001 - isolate the offender: one request at a time, each with its own outcome
+            for o, f, t in group:
+                try:
+                    self._finish(f, t, policy.select_action(o))
+                except Exception as e:  # noqa: BLE001
+                    self._finish(f, t, exc=e)
+            return
+        for (_, f, t), r in zip(group, results):
+            if isinstance(r, BaseException):
+                self._finish(f, t, exc=r)
+            else:
+                self._finish(f, t, r)
+
+    def _run_control(self, kind, payload, fut: Future, counted: bool = False):
+        """Barrier: wait until no replica runs a group, then apply the message to every replica."""
+        with self._lock:
+            if not counted:
+                self._control_pending += 1
+            while self._inflight > 0 and not self._stop.is_set():
+                self._lock.wait(timeout=0.05)
+        try:
+            fut.set_result(self._control(kind, payload))
+        except Exception as e:  # noqa: BLE001
+            fut.set_exception(e)
+        finally:
+            with self._lock:
+                self._control_pending -= 1
+                self._lock.notify_all()
 
     def _control(self, kind, payload):
         if kind == "switch":
-            self._policy.switch_model(payload)
+            for p in self._policies:
+                p.switch_model(payload)
+                if self._max_batch > 1 and hasattr(p, "warmup"):
+                    p.warmup(self._max_batch)
             self.logger.info(f"Loaded new model checkpoint: {payload}")
             return {"status": "model switched"}
-        self._policy.reset()
+        for p in self._policies:
+            p.reset()
         return {"status": "reset"}
-
-    @staticmethod
-    def _run(fut: Future, fn):
-        try:
-            fut.set_result(fn())
-        except Exception as e:  # noqa: BLE001
-            fut.set_exception(e)
 
     async def _submit(self, kind, payload):
         fut: Future = Future()
-        self._queue.put((kind, payload, fut))
+        self._queue.put((kind, payload, fut, time.monotonic()))
         return await asyncio.wrap_future(fut)
 
     # ---- one connection ----------------------------------------------------------------------------------------------

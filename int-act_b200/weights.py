@@ -136,6 +136,65 @@ def random_state_dict(d: Dims, device="cpu", seed: int = 0, dtype=torch.bfloat16
     return out
 
 
+LM_HEAD = PG + "language_model.lm_head.weight"
+NORM_ROOTS = ("normalize_inputs.", "normalize_targets.", "unnormalize_outputs.")
+
+
+def split_checkpoint(sd: Dict[str, torch.Tensor]):
+    """A lerobot checkpoint holds the module weights plus the Normalize / Unnormalize buffers
+    (`normalize_inputs.buffer_<key with . -> _>.{mean,std,min,max}`, call sites [mirror] modeling_mvla.py:243-249).
+    Returns (weights, buffers) with buffers = {root: {buffer_name: {stat: tensor}}}; the input dict is not modified."""
+    weights, buffers = {}, {}
+    for k, v in sd.items():
+        root = next((r for r in NORM_ROOTS if k.startswith(r + "buffer_")), None)
+        if root is None:
+            weights[k] = v
+            continue
+        name, stat = k[len(root) + len("buffer_"):].rsplit(".", 1)
+        buffers.setdefault(root[:-1], {}).setdefault(name, {})[stat] = v
+    return weights, buffers
+
+
+def stats_from_buffers(buffers, input_features, output_features):
+    """dataset_stats {feature key: {stat: tensor}} from the checkpoint's normalisation buffers; buffers still at their
+    +inf placeholder (a checkpoint saved before any statistics were set) are skipped."""
+    stats = {}
+    for root, feats in (("normalize_inputs", input_features), ("unnormalize_outputs", output_features),
+                        ("normalize_targets", output_features)):
+        for key in feats:
+            b = buffers.get(root, {}).get(key.replace(".", "_"))
+            if b and all(torch.isfinite(t.float()).all() for t in b.values()):
+                stats.setdefault(key, {}).update({k: t.detach().float().cpu() for k, t in b.items()})
+    return stats
+
+
+def canonical_state_dict(sd: Dict[str, torch.Tensor], strict: bool = False) -> Dict[str, torch.Tensor]:
+    """Checks a checkpoint against the key / shape table of the architecture and returns the weights the packer needs.
+    * `...language_model.lm_head.weight` stands in for a missing `embed_tokens.weight`: PaliGemma ties the two and
+      safetensors keeps only one name of a shared tensor (a checkpoint saved with the head still attached);
+    * normalisation buffers are dropped (see split_checkpoint / stats_from_buffers);
+    * missing keys and shape mismatches raise with the offending names; unexpected keys raise only when `strict`
+      (the reference loads with strict=False, policy_wrapper.py:159-162)."""
+    sd, _ = split_checkpoint(sd)
+    emb = LM + "embed_tokens.weight"
+    if emb not in sd and LM_HEAD in sd:
+        sd = dict(sd)
+        sd[emb] = sd[LM_HEAD]
+    if emb not in sd:
+        raise KeyError(f"checkpoint holds neither {emb} nor {LM_HEAD}")
+    expected = state_dict_shapes(infer_dims(sd))
+    missing = [k for k in expected if k not in sd]
+    if missing:
+        raise KeyError(f"checkpoint is missing {len(missing)} tensors, e.g. {missing[:4]}")
+    bad = [(k, tuple(sd[k].shape), expected[k]) for k in expected if tuple(sd[k].shape) != tuple(expected[k])]
+    if bad:
+        raise ValueError(f"{len(bad)} tensors have unexpected shapes, e.g. {bad[:3]}")
+    extra = [k for k in sd if k not in expected and k != LM_HEAD and not k.endswith("lm_head.weight")]
+    if strict and extra:
+        raise KeyError(f"unexpected keys in checkpoint (strict=True), e.g. {extra[:4]}")
+    return sd
+
+
 def infer_dims(sd: Dict[str, torch.Tensor]) -> Dims:
     n_sig = 0
     while f"{VT}encoder.layers.{n_sig}.layer_norm1.weight" in sd:
@@ -143,7 +202,8 @@ def infer_dims(sd: Dict[str, torch.Tensor]) -> Dims:
     n_gem = 0
     while f"{LM}layers.{n_gem}.input_layernorm.weight" in sd:
         n_gem += 1
-    return Dims(n_siglip_layers=n_sig, n_gemma_layers=n_gem, vocab=sd[LM + "embed_tokens.weight"].shape[0])
+    emb = sd[LM + "embed_tokens.weight"] if LM + "embed_tokens.weight" in sd else sd[LM_HEAD]
+    return Dims(n_siglip_layers=n_sig, n_gemma_layers=n_gem, vocab=emb.shape[0])
 
 
 def euler_times(num_steps: int) -> List[float]:
@@ -185,6 +245,9 @@ class PackedWeights:
                  max_pos: int = 2048, free_source: bool = False):
         self.device = torch.device(device)
         self.act = act_dtype
+        if LM + "embed_tokens.weight" not in sd and LM_HEAD in sd:  # tied head saved under its other name
+            sd = dict(sd)
+            sd[LM + "embed_tokens.weight"] = sd[LM_HEAD]
         self.dims = infer_dims(sd)
         d = self.dims
         self.keep: List[torch.Tensor] = []

@@ -173,6 +173,23 @@ def main():
                         full_corner=res_full[0, :, :4, :4].numpy(), eef=eef, raw=raw, state=state, acts=acts, env=env,
                         p01=np.array(stats["proprio"]["p01"]), p99=np.array(stats["proprio"]["p99"]),
                         a01=np.array(stats["action"]["p01"]), a99=np.array(stats["action"]["p99"]))
+    # ---- adapt_to_pi_aloha (modeling_mvla.py:166-218,409-425): the reference's gripper / joint-flip maps, executed here ----
+    al = extract(f"{REF}/src/model/mvla/modeling_mvla.py",
+                 ["normalize", "unnormalize", "safe_arcsin", "aloha_gripper_to_angular", "aloha_gripper_from_angular"])
+    st_in = torch.rand(3, 14, generator=torch.Generator().manual_seed(11), dtype=torch.float32)
+    st_out = st_in.clone()
+    for m in [1, 2, 8, 9]:
+        st_out[:, m] *= -1
+    for m in [6, 13]:
+        st_out[:, m] = al["aloha_gripper_to_angular"](st_out[:, m])
+    ac_in = torch.rand(3, 5, 14, generator=torch.Generator().manual_seed(12), dtype=torch.float32) * 2 - 1
+    ac_out = ac_in.clone()
+    for m in [1, 2, 8, 9]:
+        ac_out[:, :, m] *= -1
+    for m in [6, 13]:
+        ac_out[:, :, m] = al["aloha_gripper_from_angular"](ac_out[:, :, m])
+    np.savez_compressed(f"{OUT}/aloha.npz", state_in=st_in.numpy(), state_out=st_out.numpy(), act_in=ac_in.numpy(),
+                        act_out=ac_out.numpy())
     print("golden fixtures written to", OUT)
 
 

@@ -146,3 +146,82 @@ def test_bench_batch1_roofline_per_phase():
     assert abs(flops - mod.flops_per_chunk(1, 72, 4)) <= 1e-6 * flops
     by = sum(v["hbm_ms"] for v in ph.values()) * 1e-3 * peaks["hbm_gbs"] * 1e9
     assert abs(by - mod.bytes_per_chunk_b1(1, 72, 4)) <= 1e-6 * by
+
+
+# ---- round 2: checkpoint canonicalisation, normalisation buffers, empty cameras, pi-aloha maps ---------------------------
+REF_BRIDGE_JSON = "/root/reference/config/models/pi0_finetune_bridge.json"
+REF_HF_JSON = "/root/reference/config/models/hf_pi0.json"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BRIDGE_JSON), reason="reference tree not mounted")
+def test_reference_config_files_load_and_match_the_restated_keys():
+    import json
+
+    ref = json.load(open(REF_BRIDGE_JSON))
+    assert ref == BRIDGE_JSON, {k for k in set(ref) | set(BRIDGE_JSON) if ref.get(k) != BRIDGE_JSON.get(k)}
+    cfg = PI0Config.from_json(REF_BRIDGE_JSON)
+    assert cfg.n_cams == 1 and cfg.tokenizer_max_length == 72
+    hf = PI0Config.from_json(REF_HF_JSON)   # the stock lerobot pi0 config: 3 cameras, MEAN_STD state / action
+    hf.validate_features()
+    assert hf.n_cams == 3 + hf.empty_cameras and hf.normalization_mapping["STATE"] == "MEAN_STD"
+
+
+def test_validate_features_adds_empty_camera_placeholders_once():
+    cfg = bridge_config(empty_cameras=2)
+    assert cfg.n_cams == 1
+    cfg.validate_features()
+    cfg.validate_features()   # idempotent
+    assert cfg.n_cams == 3 and "observation.images.empty_camera_1" in cfg.image_features
+    again = PI0Config.from_dict(cfg.to_dict())   # a config.json that already lists the placeholders
+    again.validate_features()
+    assert again.n_cams == 3
+
+
+def test_checkpoint_with_tied_lm_head_and_mean_std_buffers(tmp_path):
+    from int_act_b200.policy import PI0Policy
+
+    dims = W.Dims(n_siglip_layers=1, n_gemma_layers=1, vocab=64)
+    sd = W.random_state_dict(dims, seed=4)
+    emb = sd.pop(W.LM + "embed_tokens.weight")          # saved with the PaliGemma head still tied: only lm_head survives
+    sd[W.LM_HEAD] = emb
+    sd["model.paligemma_with_expert.gemma_expert.lm_head.weight"] = torch.zeros(8, 1024, dtype=torch.bfloat16)
+    mean, std = torch.arange(7.0), torch.arange(7.0) * 0.1 + 0.5
+    for root in ("normalize_inputs.buffer_observation_state", "unnormalize_outputs.buffer_action",
+                 "normalize_targets.buffer_action"):
+        sd[root + ".mean"], sd[root + ".std"] = mean.clone(), std.clone()
+    ok = W.canonical_state_dict(sd)
+    assert torch.equal(ok[W.LM + "embed_tokens.weight"], emb) and not any(k.startswith("normalize") for k in ok)
+    assert W.infer_dims(ok).vocab == 64
+    with pytest.raises(KeyError, match="unexpected keys"):
+        W.canonical_state_dict({**sd, "model.bogus.weight": torch.zeros(1)}, strict=True)
+    broken = dict(sd)
+    del broken["model.state_proj.bias"]
+    with pytest.raises(KeyError, match="missing 1 tensors"):
+        W.canonical_state_dict(broken)
+    wrong = {**sd, "model.state_proj.bias": torch.zeros(3)}
+    with pytest.raises(ValueError, match="unexpected shapes"):
+        W.canonical_state_dict(wrong)
+    # end to end through from_pretrained: the statistics come out of the checkpoint, as in lerobot
+    W.save_safetensors(sd, str(tmp_path))
+    cfg = bridge_config(normalization_mapping={"VISUAL": "IDENTITY", "STATE": "MEAN_STD", "ACTION": "MEAN_STD"})
+    pol = PI0Policy.from_pretrained(str(tmp_path), config=cfg)
+    x = torch.ones(2, 7)
+    got = pol.normalize_inputs({"observation.state": x})["observation.state"]
+    assert torch.allclose(got, (x - mean) / (std + 1e-8))
+    back = pol.unnormalize_outputs({"action": torch.ones(2, 4, 7)})["action"]
+    assert torch.allclose(back, torch.ones(2, 4, 7) * std + mean)
+    with pytest.raises(ValueError, match="needs dataset_stats"):   # MEAN_STD without statistics anywhere: loud
+        PI0Policy(cfg, None, state_dict=ok)
+
+
+def test_pi_aloha_maps_match_the_reference_functions():
+    import numpy as np
+
+    from int_act_b200.policy import pi_aloha_decode_state, pi_aloha_encode_actions
+
+    d = np.load(os.path.join(ROOT, "tests", "golden", "aloha.npz"))
+    s_in = torch.from_numpy(d["state_in"])
+    keep = s_in.clone()
+    assert torch.equal(pi_aloha_decode_state(s_in), torch.from_numpy(d["state_out"]))
+    assert torch.equal(s_in, keep)   # the caller's tensor is not modified (the reference mutates in place)
+    assert torch.equal(pi_aloha_encode_actions(torch.from_numpy(d["act_in"])), torch.from_numpy(d["act_out"]))

@@ -215,3 +215,127 @@ def test_wrapper_select_action_semantics():
     w3.switch_model("/ckpt")
     assert w3.model is not m
     w3.reset()
+
+
+# ---- round 2: failure isolation, latency histogram, replicas behind one port, reference-style construction ---------------
+def test_one_bad_request_in_a_coalesced_group_only_fails_its_own_connection():
+    pol = FakePolicy()
+    bad_many = pol.select_action_many
+
+    def many(obs_list):   # like the real wrapper: a malformed observation makes the whole batched call raise
+        if any(o.get("boom") for o in obs_list):
+            raise RuntimeError("kaboom")
+        return bad_many(obs_list)
+
+    pol.select_action_many = many
+    with ServerThread(pol, max_batch=4, batch_window_ms=300.0) as srv:
+        good = [WebsocketPolicyClient("127.0.0.1", srv.bound_port) for _ in range(2)]
+        bad = WebsocketPolicyClient("127.0.0.1", srv.bound_port)
+        out, err = [None, None], []
+
+        def run_bad():
+            try:
+                bad.infer({"boom": True})
+            except RuntimeError as e:
+                err.append(str(e))
+
+        ts = [threading.Thread(target=lambda i=i: out.__setitem__(i, good[i].infer(obs_for(float(i + 1))))) for i in range(2)]
+        ts.append(threading.Thread(target=run_bad))
+        [t.start() for t in ts]
+        [t.join(20) for t in ts]
+        assert np.all(out[0] == 1.0) and np.all(out[1] == 2.0)           # co-batched clients are unharmed
+        assert len(err) == 1 and "kaboom" in err[0]
+        assert srv.stats["failed_requests"] == 1
+        lat = srv.latency_ms()
+        assert lat["n"] == 3 and lat["p50"] > 0 and lat["p99"] >= lat["p50"]
+        assert np.all(good[0].infer(obs_for(7.0)) == 7.0)                 # and keep their connection
+        [c.close() for c in good]
+
+
+def test_replicas_share_one_port_and_controls_reach_every_replica():
+    pols = [FakePolicy() for _ in range(3)]
+    import time as _t
+    for p in pols:   # make inference slow enough that the other replicas pick up work
+        orig = p.select_action
+        p.select_action = lambda obs, orig=orig: (_t.sleep(0.05), orig(obs))[1]
+    n = 9
+    with ServerThread(pols[0], replicas=pols[1:]) as srv:
+        clients = [WebsocketPolicyClient("127.0.0.1", srv.bound_port) for _ in range(n)]
+        out = [None] * n
+        ts = [threading.Thread(target=lambda i=i: out.__setitem__(i, clients[i].infer(obs_for(float(i))))) for i in range(n)]
+        [t.start() for t in ts]
+        [t.join(20) for t in ts]
+        for i in range(n):
+            assert np.all(out[i] == float(i))
+        assert srv.stats["replicas"] == 3 and sum(srv.stats["per_replica_batches"]) == n
+        assert sum(1 for b in srv.stats["per_replica_batches"] if b > 0) >= 2     # more than one GPU did work
+        assert clients[0].reset() == {"status": "reset"} and [p.resets for p in pols] == [1, 1, 1]
+        assert clients[1].switch_model("/ckpt/a") == {"status": "model switched"}
+        assert [p.switched for p in pols] == [["/ckpt/a"]] * 3
+        [c.close() for c in clients]
+
+
+def test_wrapper_reference_constructor_starts_without_a_model_and_loads_on_switch():
+    from types import SimpleNamespace
+
+    loaded = []
+
+    class FakePI0:
+        @classmethod
+        def from_pretrained(cls, pretrained_name_or_path, config=None, **kw):
+            loaded.append((pretrained_name_or_path, config))
+            m = FakeModel()
+            m.model = SimpleNamespace(paligemma_with_expert=SimpleNamespace(
+                gemma_expert=SimpleNamespace(lm_head=1), paligemma=SimpleNamespace(language_model=SimpleNamespace(lm_head=1))))
+            m.to = lambda a, m=m: m
+            m.eval = lambda m=m: m
+            return m
+
+    cfg = SimpleNamespace(seed=42, debug=False, gpu_id=0, use_amp=True, use_bf16=True, freeze_lm_head=True,
+                          model_cfg=SimpleNamespace(type="pi0"),
+                          eval_cfg=SimpleNamespace(action_step=4, port=8000, host="0.0.0.0",
+                                                   env_adapter_path="src.experiments.env_adapters.simpler.BridgeSimplerAdapter"))
+    w = LeRobotPolicyWrapper(pipeline_cfg=cfg, model_class=FakePI0)
+    assert w.model is None and w.env_adapter is None and w.action_step == 4
+    with pytest.raises(ValueError, match="Model is not initialized"):
+        w.reset()
+    with pytest.raises(ValueError, match="Model is not initialized"):
+        w.select_action(obs_for(1.0))
+    w._initialize_env_adapter = lambda: FakeAdapter()     # the real one needs a CUDA device
+    w.switch_model("/ckpt/step_1513")
+    assert loaded == [("/ckpt/step_1513", cfg.model_cfg)]
+    assert w.model.model.paligemma_with_expert.gemma_expert.lm_head is None            # freeze_lm_head
+    assert w.select_action(obs_for(2.0)).shape == (4, 7)
+    from int_act_b200.serving.policy_wrapper import resolve_adapter_class
+    from int_act_b200 import adapters
+    assert resolve_adapter_class("src.experiments.env_adapters.simplerMS3.BridgeSimplerBatchAdapter") is adapters.BridgeSimplerBatchAdapter
+    with pytest.raises(ValueError):
+        resolve_adapter_class("src.experiments.env_adapters.libero.NoSuchAdapter")
+
+
+REF_YAML = "/root/reference/config/experiment/simpler/pi0_finetune_bridge_ev.yaml"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_YAML), reason="reference tree not mounted")
+def test_launcher_builds_the_server_from_the_reference_yaml():
+    from int_act_b200.pipeline import PipelineConfig, parse_overrides
+    from int_act_b200.serve import build_server
+
+    over = parse_overrides(["--eval_cfg.port", "8123", "--use_bf16=False", "--eval_cfg.env_adapter", "BridgeSimplerBatchAdapter"])
+    cfg = PipelineConfig.from_yaml(REF_YAML, over)
+    assert cfg.eval_cfg.port == 8123 and cfg.use_bf16 is False and cfg.seed == 42
+    assert cfg.eval_cfg.env_adapter_path == "src.experiments.env_adapters.simpler.BridgeSimplerBatchAdapter"
+    assert cfg.model_cfg.tokenizer_max_length == 72 and cfg.model_cfg.n_action_steps == 4
+    assert os.path.exists(cfg.env.dataset_statistics_path)
+    server, wrappers, _ = build_server(["--config_path", REF_YAML, "--eval_cfg.port", "0", "--eval_cfg.host", "127.0.0.1",
+                                        "--server.max_batch", "4"])
+    assert len(wrappers) == 1 and wrappers[0].model is None and wrappers[0].action_step == 4
+    # the reference's unmodified flow: connect, reset before any model -> the server reports the error over the wire
+    st = ServerThread.__new__(ServerThread)
+    st.server, st.ready, st.thread = server, threading.Event(), None
+    st.thread = threading.Thread(target=st._main, daemon=True)
+    with st as srv:
+        c = WebsocketPolicyClient("127.0.0.1", srv.bound_port)
+        assert c.get_server_metadata()["model"] == "pi0"
+        with pytest.raises(RuntimeError, match="Model is not initialized"):
+            c.reset()
