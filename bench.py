@@ -348,16 +348,21 @@ def b200_arm(args, rank, world, local_rank):
 
     # ---- weights: generated once on rank 0, broadcast over NCCL/NVLink ------------------
     dims = Dims()
-    if rank == 0:
-        sd = random_state_dict(dims, device=dev, seed=0)
-    else:
-        sd = {k: torch.empty(s, dtype=torch.bfloat16, device=dev) for k, s in state_dict_shapes(dims).items()}
+    sd = random_state_dict(dims, device=dev, seed=0) if rank == 0 else None
+    bcast_gbs = None
     if world > 1:
+        from int_act_b200.sharding import broadcast_state_dict_blob
+
+        warm = torch.zeros(1 << 20, device=dev)
+        for _ in range(2):           # communicator set-up / NVLink channel warm-up outside the timed broadcast
+            dist.broadcast(warm, src=0)
+        torch.cuda.synchronize()
+        dist.barrier()
         t0 = time.perf_counter()
-        for k in sd:
-            dist.broadcast(sd[k], src=0)
+        sd = broadcast_state_dict_blob(sd, state_dict_shapes(dims), torch.bfloat16, dev, src=0)
         torch.cuda.synchronize()
         bcast_s = time.perf_counter() - t0
+        bcast_gbs = sum(v.numel() for v in sd.values()) * 2 / bcast_s / 1e9
     else:
         bcast_s = 0.0
     policy = PI0Policy(make_config(args.workload), state_dict=sd, max_batch=B, device=dev)
@@ -407,17 +412,76 @@ def b200_arm(args, rank, world, local_rank):
     launches = eng.launches_per_infer.get(B, 0) * K
 
     # ---- (2) end to end through the public API with pinned host buffers ----------------------------------------
+    # N = 1: PI0Policy.infer_action on the host batch. N > 1: sharding.sharded_infer - every rank holds the same
+    # [B * N]-observation host batch, runs its contiguous shard and the chunks are gathered over NCCL, so the gathered
+    # [B * N, H, 7] array on rank 0's host is INSIDE the timed region.
+    if world > 1:
+        from int_act_b200.sharding import sharded_infer
+
+        full = synthetic_observations(B * world, n_cams, lang_len, seed=1234, pinned=True)
+
+        def e2e_step():
+            return sharded_infer(policy.infer_action, full).cpu()
+        h2d = sum(v.numel() * v.element_size() for v in full.values()) // world
+        e2e_shape = (B * world, horizon, 7)
+    else:
+        def e2e_step():
+            return policy.infer_action(obs).cpu()   # H2D of the observation, the path, D2H of the chunk
+        e2e_shape = (B, horizon, 7)
     for _ in range(max(1, min(W, 2))):
-        policy.infer_action(obs).cpu()
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(K):
-        out = policy.infer_action(obs).cpu()   # H2D of the observation, the path, D2H of the chunk
+        out = e2e_step()
     torch.cuda.synchronize()
     e2e_s = reduce_max(time.perf_counter() - t0)
     barrier()
     e2e_value = world * B * K / e2e_s
-    assert out.shape == (B, horizon, 7) and torch.isfinite(out).all()
+    assert out.shape == e2e_shape and torch.isfinite(out).all()
+
+    # ---- (2b) the other BASELINE configurations (SURVEY.md 8d "Concrete configs"), all ranks, device-timed ----------------
+    # C3 strong split: 64 observations TOTAL (64 / N per GPU); C4 rephrase: 256 total; C5 LIBERO-shaped: 512 total.
+    configs = {}
+    if not args.no_configs:
+        from int_act_b200.engine import Pi0Engine
+
+        plan = [("c3_bridge_strong", "bridge", 64), ("c4_rephrase", "rephrase", 256), ("c5_libero", "libero", 512)]
+        for name, wl, total in plan:
+            per_gpu = max(1, total // world)
+            if name == "c3_bridge_strong" and world == 1 and args.workload == "bridge" and B == 64:
+                configs[name] = {"total_batch": 64, "batch_per_gpu": 64, "value": value, "unit": "chunks/s",
+                                 "ms_per_step": ms_per_step, "same_as": "headline"}
+                continue
+            nc, ll, hz = WORKLOADS[wl]
+            e = Pi0Engine(eng.packed, n_cams=nc, lang_len=ll, horizon=hz, max_batch=per_gpu)
+            ob = synthetic_observations(per_gpu, nc, ll, seed=4321 + rank, pinned=False)
+            imgs = [ob[k].to(dev) for k in ob if k.startswith("observation.images")]
+            e.sample_actions(imgs, [torch.ones(per_gpu, dtype=torch.bool, device=dev) for _ in imgs],
+                             ob["lang_tokens"].to(dev), ob["lang_masks"].to(dev), ob["observation.state"].to(dev))
+            stc = e._static(per_gpu)
+            for _ in range(2):
+                stc["x_t"].normal_()
+                e._run_static(per_gpu)
+            barrier()
+            kc = max(2, min(K, 5))
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(kc):
+                stc["x_t"].normal_()
+                e._run_static(per_gpu)
+            b.record()
+            torch.cuda.synchronize()
+            ms = reduce_max(a.elapsed_time(b)) / kc
+            barrier()
+            v = per_gpu * world / (ms * 1e-3)
+            tfl = flops_per_chunk(nc, ll, hz) * per_gpu / (ms * 1e-3) / 1e12
+            configs[name] = {"total_batch": per_gpu * world, "batch_per_gpu": per_gpu, "value": v, "unit": "chunks/s",
+                             "ms_per_step": ms, "steps": kc, "achieved_tflops_per_gpu": tfl,
+                             "frac_of_sustained_peak": tfl / peaks["bf16_tflops_sustained"],
+                             "launches_per_infer": e.launches_per_infer.get(per_gpu)}
+            del e, stc
+            torch.cuda.empty_cache()
 
     line = {
         "metric": "pi0_action_chunks_per_sec", "value": value, "unit": "chunks/s", "n_gpus": world, "steps": K,
@@ -428,12 +492,15 @@ def b200_arm(args, rank, world, local_rank):
                    "prefix_tokens": n_cams * 256 + lang_len, "horizon": horizon, "num_steps": 10,
                    "parallelism": f"dp{world} (rollout batch sharded, no collective in the forward)",
                    "l2": "inputs larger than L2: every step streams 5.9 GB of weights plus >1 GB of activations "
-                         "through the 126 MB L2", "weights_broadcast_s": round(bcast_s, 3)},
+                         "through the 126 MB L2", "weights_broadcast_s": round(bcast_s, 4),
+                   "weights_broadcast_gbs": None if bcast_gbs is None else round(bcast_gbs, 1)},
         "e2e": {"value": e2e_value, "unit": "chunks/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": 1e3 * e2e_s / K},
         "gpu_launches": launches,
         "clocks": clocks,
     }
+    if configs:
+        line["configs"] = configs
 
     if rank == 0:
         # ---- (3) roofline of the dominant kernel, CUDA-event pair around every launch of one eager step -------------
@@ -571,6 +638,7 @@ def main():
     ap.add_argument("--latency-iters", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-eager", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C3-strong / C4 / C5 side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -31,6 +31,11 @@ class Pi0Engine:
             raise pb.Pi0Error(f"weights packed as {packed.act}, engine dtype {self.act}")
         if packed.num_steps != num_steps:
             raise pb.Pi0Error("weights were packed for a different num_steps (time bias table)")
+        # `tokenizer_max_length` is a free config key in the reference (pi0_finetune_bridge.json:46); the kernels want the
+        # text block in multiples of 8 tokens. Extra positions are padding with mask 0: masked keys get probability
+        # exp(-2.38e38 - max) == 0 exactly and position ids are cumsum(pad) - 1, so the result is bit-identical.
+        self.lang_len_user = lang_len
+        lang_len = (lang_len + 7) // 8 * 8
         self.n_cams, self.lang_len, self.horizon, self.num_steps = n_cams, lang_len, horizon, num_steps
         self.max_batch = max_batch
         self.P = n_cams * 256 + lang_len
@@ -156,8 +161,14 @@ class Pi0Engine:
         for dst, src in zip(st["images"], images):
             dst.copy_(src.to(torch.float32), non_blocking=True)
         st["img_masks"].copy_(torch.stack([m.reshape(B) for m in img_masks]).to(torch.uint8), non_blocking=True)
-        st["tokens"].copy_(lang_tokens, non_blocking=True)
-        st["lang_masks"].copy_(lang_masks.to(torch.uint8), non_blocking=True)
+        L = lang_tokens.shape[1]
+        if L != self.lang_len_user:
+            raise pb.Pi0Error(f"{L} text positions given, engine built for tokenizer_max_length {self.lang_len_user}")
+        if L != self.lang_len:
+            st["tokens"].zero_()
+            st["lang_masks"].zero_()
+        st["tokens"][:, :L].copy_(lang_tokens, non_blocking=True)
+        st["lang_masks"][:, :L].copy_(lang_masks.to(torch.uint8), non_blocking=True)
         st["state"].zero_()
         st["state"][:, : state.shape[1]].copy_(state.to(torch.float32), non_blocking=True)  # pad_vector
         if noise is None:

@@ -56,7 +56,7 @@ def test_small_depth_parity(cuda, mode):
     print(f"\n[small depth {mode}] k0 err {kerr:.3e}  action err {err:.3e}  |ref|max {ref.abs().max().item():.3f} "
           f"|ref-noise|max {(ref - inp[5]).abs().max().item():.3f}")
     assert err <= TOL[mode], err
-    assert ref.abs().max().item() > 0.1  # the comparison is not vacuous
+    assert (ref - inp[5]).abs().max().item() > 0.3  # the model moved the noise: the comparison is not vacuous
 
 
 def test_cuda_graph_replay_matches_eager_launches(cuda):

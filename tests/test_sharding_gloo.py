@@ -13,7 +13,8 @@ import torch.multiprocessing as mp
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from int_act_b200.sharding import broadcast_state_dict, shard_batch, shard_bounds, sharded_infer  # noqa: E402
+from int_act_b200.sharding import (broadcast_state_dict, broadcast_state_dict_blob, shard_batch, shard_bounds,  # noqa: E402
+                                   sharded_infer)
 
 
 def _free_port():
@@ -47,6 +48,10 @@ def _worker(rank, world, port, n_obs, q):
         sd = {k: torch.full(s, float(i + 1)) for i, (k, s) in enumerate(sorted(shapes.items()))} if rank == 0 else None
         got = broadcast_state_dict(sd, shapes, torch.float32, "cpu")
         ok_bcast = all(torch.equal(got[k], torch.full(shapes[k], float(i + 1))) for i, k in enumerate(sorted(shapes)))
+        for pieces in (1, 3):   # the one-blob broadcast (what bench.py uses at N > 1)
+            blob = broadcast_state_dict_blob(sd, shapes, torch.float32, "cpu", pieces=pieces)
+            ok_bcast = ok_bcast and all(torch.equal(blob[k], torch.full(shapes[k], float(i + 1)))
+                                        for i, k in enumerate(sorted(shapes))) and blob["a.weight"].shape == (4, 3)
         out = sharded_infer(_fake_infer, batch)
         full = _fake_infer(batch)
         q.put((rank, ok_bcast, torch.equal(out, full), tuple(out.shape)))
