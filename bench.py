@@ -477,7 +477,7 @@ def b200_arm(args, rank, world, local_rank):
             v = per_gpu * world / (ms * 1e-3)
             tfl = flops_per_chunk(nc, ll, hz) * per_gpu / (ms * 1e-3) / 1e12
             configs[name] = {"total_batch": per_gpu * world, "batch_per_gpu": per_gpu, "value": v, "unit": "chunks/s",
-                             "ms_per_step": ms, "steps": kc, "achieved_tflops_per_gpu": tfl,
+                             "ms_per_step": ms, "steps": kc, "achieved_tflops_per_gpu": tfl, "paths": e.path_report(per_gpu),
                              "frac_of_sustained_peak": tfl / peaks["bf16_tflops_sustained"],
                              "launches_per_infer": e.launches_per_infer.get(per_gpu)}
             del e, stc
@@ -501,6 +501,7 @@ def b200_arm(args, rank, world, local_rank):
     }
     if configs:
         line["configs"] = configs
+    line["paths"] = {f"batch_{B}": eng.path_report(B), "batch_1": eng.path_report(1)}
 
     if rank == 0:
         # ---- (3) roofline of the dominant kernel, CUDA-event pair around every launch of one eager step -------------

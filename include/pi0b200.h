@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PI0_ABI_VERSION 2
+#define PI0_ABI_VERSION 3
 
 #define PI0_SIGLIP_LAYERS 27
 #define PI0_GEMMA_LAYERS 18
@@ -146,6 +146,13 @@ const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems);
  * recorded events; the product path leaves profiling off. */
 int pi0_profile(pi0_ctx* ctx, int enable);
 int pi0_profile_report(pi0_ctx* ctx, char* buf, size_t buf_bytes);
+
+/* Which kernel variant each phase of pi0_infer takes at batch B with this ctx, as one JSON object: {"gemm", "siglip_attention",
+ * "prefill_attention", "denoise", "denoise_attention", ...}. The reference has one eager path
+ * (config/models/pi0_finetune_bridge.json:50 "attention_implementation": "eager"); here shape limits select between
+ * fused and per-op kernels (P <= 336 for the fused prefix attention, M = B*S <= 16 for the persistent denoise kernel, ...):
+ * this call makes every such fallback visible. Host only, no launch. */
+int pi0_path_report(pi0_ctx* ctx, int B, char* buf, size_t buf_bytes);
 
 /* kernels launched by this library since the last call with reset != 0 (bench "gpu_launches") */
 long long pi0_launch_count(int reset);

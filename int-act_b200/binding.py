@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("PI0_LIB") or os.path.join(_HERE, "libpi0b200.so")  # 
 
 SIGLIP_LAYERS = 27
 GEMMA_LAYERS = 18
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 c_f32p = C.c_void_p  # device pointers are opaque to ctypes
 c_ptr = C.c_void_p
@@ -92,6 +92,7 @@ SIGNATURES = {
     "pi0_debug_buffer": (c_ptr, [c_ptr, C.c_char_p, C.POINTER(C.c_int64)]),
     "pi0_profile": (C.c_int, [c_ptr, C.c_int]),
     "pi0_profile_report": (C.c_int, [c_ptr, C.c_char_p, C.c_size_t]),
+    "pi0_path_report": (C.c_int, [c_ptr, C.c_int, C.c_char_p, C.c_size_t]),
     "pi0_launch_count": (C.c_longlong, [C.c_int]),
     "pi0_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_int, C.c_int, c_ptr]),
     "pi0_rmsnorm": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),

@@ -490,6 +490,51 @@ int pi0_profile_report(pi0_ctx* c, char* buf, size_t buf_bytes) {
   return 0;
 }
 
+int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
+  // Which kernel variant every phase of pi0_infer takes at batch B with this ctx: the same predicates as gemma_layer /
+  // pi0_siglip_forward / pi0_denoise_loop, so that silent fallbacks (P > 336, P + S > 352, S > 16, fp32 ...) are visible.
+  PI0_TRY(check_batch(c, B));
+  PI0_REQUIRE(buf != nullptr && buf_bytes > 2, "pi0_path_report: bad arguments");
+  const bool bf = c->cfg.dtype == 0 && c->cfg.gemm_impl == 0;
+  const int S = c->S, P = c->P, M = B * S;
+  const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
+  const char* gemm = c->cfg.dtype == 1 || c->cfg.gemm_impl == 1 ? "simt_fp32_check" : "tcgen05";
+  const char* siglip_attn = bf && c->siglip_fused ? "fused_mma_sync" : "gemm_softmax_gemm";
+  const bool pf = bf && c->prefill_fused && prefill_attention_supported(P, P) &&
+                  (int64_t)B * ((P * kHeads + 127) / 128) >= c->prefill_fused_min_tiles;
+  const char* prefill_attn = pf ? "fused_tcgen05" : "gemm_softmax_gemm";
+  const char* denoise;
+  const char* denoise_attn;
+  if (c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(M, S, P, c->mega_ctas)) {
+    denoise = c->loop_mode == 2 ? "loop_kernel_whole_euler_loop" : "loop_kernel_per_step";
+    denoise_attn = "in_kernel";
+  } else if (c->mega_ctas > 0 && mega_supported(M, S, P)) {
+    denoise = "persistent_layers_kernel_per_step";
+    denoise_attn = "in_kernel";
+  } else if (bf && skinny_supported(M) && S <= 48 && P + S <= 640) {
+    denoise = "skinny_mma_sync_per_op";
+    denoise_attn = "fused_single_cta";
+  } else {
+    denoise = bf ? "tcgen05_per_op" : "simt_fp32_check";
+    if (bf && S <= 48 && P + S <= 640) {
+      if (B > 12 && c->attn_split && decode_attention_batch_supported(S, P)) denoise_attn = "batch_cta_pair_per_sample";
+      else if (B >= 4 && c->attn_split && decode_attention_split_supported(S, P)) denoise_attn = "split_two_launches";
+      else denoise_attn = "fused_single_cta";
+    } else {
+      denoise_attn = "gemm_softmax_gemm";
+    }
+  }
+  char tmp[640];
+  const int n = snprintf(tmp, sizeof(tmp),
+                         "{\"batch\": %d, \"prefix_tokens\": %d, \"suffix_tokens\": %d, \"sms\": %d, \"gemm\": \"%s\", "
+                         "\"siglip_attention\": \"%s\", \"prefill_attention\": \"%s\", \"denoise\": \"%s\", "
+                         "\"denoise_attention\": \"%s\"}",
+                         B, P, S, sms, gemm, siglip_attn, prefill_attn, denoise, denoise_attn);
+  PI0_REQUIRE(n > 0 && (size_t)n + 1 <= buf_bytes, "pi0_path_report: buffer too small (%d needed)", n + 1);
+  memcpy(buf, tmp, (size_t)n + 1);
+  return 0;
+}
+
 const void* pi0_debug_buffer(pi0_ctx* ctx, const char* name, int64_t* n_elems) {
   if (!ctx || !name) return nullptr;
   for (int i = 0; i < ctx->nbufs; ++i) {

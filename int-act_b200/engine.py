@@ -196,6 +196,14 @@ class Pi0Engine:
             st["x_t"].copy_(keep)
         return {k: (v[0], v[1]) for k, v in json.loads(buf.value.decode()).items()}
 
+    def path_report(self, B: int) -> Dict[str, object]:
+        """Which kernel variant every phase takes at batch size B (fused vs per-op fallbacks made visible)."""
+        import json
+
+        buf = C.create_string_buffer(1024)
+        pb.check(self.lib.pi0_path_report(self.ctx, B, buf, len(buf)), "pi0_path_report")
+        return json.loads(buf.value.decode())
+
     def debug_buffer(self, name: str, dtype=None) -> torch.Tensor:
         """Copy of a named workspace buffer (parity tests)."""
         n = C.c_int64()

@@ -225,3 +225,35 @@ def test_pi_aloha_maps_match_the_reference_functions():
     assert torch.equal(pi_aloha_decode_state(s_in), torch.from_numpy(d["state_out"]))
     assert torch.equal(s_in, keep)   # the caller's tensor is not modified (the reference mutates in place)
     assert torch.equal(pi_aloha_encode_actions(torch.from_numpy(d["act_in"])), torch.from_numpy(d["act_out"]))
+
+
+def test_hf_tokenizer_known_answer_when_the_files_are_cached():
+    """prepare_language ([mirror] modeling_mvla.py:387-407): "\\n" appended, bos first, right padding to
+    tokenizer_max_length, truncation. The PaliGemma SentencePiece files are not on this box (no network), so
+    this known-answer test SKIPS here; on a machine with the tokenizer cached it pins the ids the synthetic stand-in
+    only imitates (bos = 2, "\\n" = 108, pad = 0)."""
+    from int_act_b200.policy import HFTokenizer, PI0Policy
+
+    try:
+        tok = HFTokenizer()
+    except Exception as e:  # noqa: BLE001
+        pytest.skip(f"google/paligemma-3b-pt-224 tokenizer files not cached: {type(e).__name__}")
+    pol = PI0Policy(bridge_config(), tokenizer=tok)
+    ids, mask = pol.prepare_language({"task": ["put the carrot on the plate", "stack the cube\n"]})
+    assert ids.shape == (2, 72) and mask.shape == (2, 72) and mask.dtype == torch.bool
+    n = mask.sum(1)
+    for b in range(2):
+        assert ids[b, 0].item() == 2                          # bos prepended by the tokenizer
+        assert ids[b, n[b] - 1].item() == 108                 # the trailing "\n"
+        assert mask[b, : n[b]].all() and not mask[b, n[b]:].any() and (ids[b, n[b]:] == 0).all()   # right padding
+    assert n[0].item() > n[1].item() >= 4                     # bos + sentencepiece pieces + "\n"
+    long = pol.prepare_language({"task": "word " * 200})
+    assert long[0].shape == (1, 72) and long[1].all()         # truncation=True (the fork's addition, modeling_mvla.py:402)
+
+
+def test_synthetic_tokenizer_keeps_the_call_shape():
+    from int_act_b200.policy import PI0Policy, SyntheticTokenizer
+
+    pol = PI0Policy(bridge_config(), tokenizer=SyntheticTokenizer())
+    ids, mask = pol.prepare_language({"task": "put the carrot on the plate"})
+    assert ids.shape == (1, 72) and ids[0, 0] == 2 and ids[0, mask.sum() - 1] == 108 and mask.sum() == 8

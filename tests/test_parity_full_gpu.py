@@ -159,3 +159,17 @@ def test_odd_tokenizer_max_length_is_padded_internally(cuda):
     _, out = _engine_out(cuda, sd, "bf16", 2, inp, 1, 45, 4, graph=False)
     ref = oracle_for(sd, dims, 1, 45, 4, "bf16").sample_actions(*inp)
     assert (out - ref).abs().max().item() <= 1e-2
+
+
+def test_path_report_names_the_variant_every_phase_takes(cuda):
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=1, vocab=256)
+    packed = PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.bfloat16)
+    eng = Pi0Engine(packed, max_batch=64)
+    b1, b64 = eng.path_report(1), eng.path_report(64)
+    assert b1["denoise"] == "persistent_layers_kernel_per_step" and b1["prefill_attention"] == "gemm_softmax_gemm"
+    assert b64["denoise"] == "tcgen05_per_op" and b64["denoise_attention"] == "batch_cta_pair_per_sample"
+    assert b64["prefill_attention"] == "fused_tcgen05" and b64["siglip_attention"] == "fused_mma_sync"
+    lib = Pi0Engine(packed, n_cams=2, horizon=16, max_batch=64).path_report(64)      # LIBERO shape: P = 584 > 336
+    assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "gemm_softmax_gemm"
+    f32 = Pi0Engine(PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.float32), dtype="fp32")
+    assert f32.path_report(1)["gemm"] == "simt_fp32_check"
