@@ -232,6 +232,17 @@ class BridgeSimplerBatchAdapter(_GpuAdapterBase):
         return {"observation.images.top": images, "observation.state": state, "task": obs["task"]}
 
 
+    def preprocess_many(self, obs_list) -> dict:
+        """Several requests (each a [b_i, H, W, 3] frame stack) as ONE host concatenation, one H2D copy and one resize /
+        proprio launch - the coalescing server's path. Same arithmetic per observation as `preprocess`."""
+        frames = np.concatenate([np.asarray(o["observation.images.top"]) for o in obs_list], axis=0)
+        eef = np.concatenate([np.asarray(o["observation.state"], dtype=np.float32).reshape(-1, 8) for o in obs_list], axis=0)
+        tasks = [t for o in obs_list for t in ([o["task"]] if isinstance(o["task"], str) else list(o["task"]))]
+        if frames.shape[0] != eef.shape[0] or frames.shape[0] != len(tasks):
+            raise ValueError("frames / states / tasks disagree on the number of observations")
+        return self.preprocess({"observation.images.top": frames, "observation.state": eef, "task": tasks})
+
+
 class BridgeSimplerAdapter(_GpuAdapterBase):
     """Single-observation adapter (reference: simpler.py:154-190). obs = {"observation.images.top": uint8 [H, W, 3],
     "observation.state": the simulator's nested obs dict (eef pose under ["agent"]["eef_pos"]), "task": str}."""

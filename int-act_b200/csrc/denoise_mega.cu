@@ -68,6 +68,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       : "memory");
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+// The RMSNorm gains of a phase (4 KB, first touched right after a grid barrier, i.e. a cold HBM read on the critical
+// path) are pulled into L2 by 32 threads BEFORE the barrier; costs no registers.
+__device__ __forceinline__ void prefetch_gain_l2(const float* gain) {
+  if (threadIdx.x < 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(gain + threadIdx.x * 32));
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
   unsigned long long v;
@@ -276,51 +281,75 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
   const int g = lane >> 2, t4 = lane & 3;
   int slot = 0;
   uint32_t phase = 0;
-  int parity = 0;  // double-buffered cross-warp reduction scratch
 
-  // runs this CTA's units of one GEMM phase; `epi(u, total)` is called by threads < 128 with row = tid >> 3, col = tid & 7
+  // Runs this CTA's units of one GEMM phase. Units are processed in batches (4 per batch for M <= 8 rows, 2 for M <= 16):
+  // every warp accumulates its k-slice of all the batch's chunks, then ONE cross-warp reduction + ONE CTA barrier + ONE
+  // epilogue pass serve the whole batch, the epilogues of the batch's units running side by side on disjoint thread groups
+  // (round 1 paid a reduction, a barrier and a 128-thread epilogue per unit: ~1.2 us each on the critical path, 4 units in
+  // the gate/up phase). `epi(u, row, col, t0, t1)` is called with row < M; the fp32 sum over the 8 warps keeps its fixed
+  // order, so results are bit-identical to the per-unit form.
+  constexpr int kUB = M16 ? 2 : 4;           // units per batch
+  constexpr int kRowsR = M16 ? 16 : 8;       // rows kept in the reduction scratch
+  constexpr int kEpiT = kRowsR * 8;          // epilogue threads per unit
   auto run_units = [&](int ph, auto&& epi) {
     const int nch = ph == MEGA_DOWN ? 4 : 2;
     const bool along_k = ph == MEGA_O || ph == MEGA_DOWN;
     const int16_t* t = tab + ph * (kMegaMaxUnits + 1);
     const int cnt = t[0];
-    for (int i = 0; i < cnt; ++i) {
-      const int u = t[1 + i];
-      float acc[2][4];
+    for (int i0 = 0; i0 < cnt; i0 += kUB) {
+      const int nb = min(kUB, cnt - i0);
+      float acc[kUB][2][4];
 #pragma unroll
-      for (int a = 0; a < 2; ++a)
+      for (int b = 0; b < kUB; ++b)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) acc[a][e] = 0.0f;
-      for (int ch = 0; ch < nch; ++ch) {
-        mbar_wait(&full_bar[slot], phase);
-        const bf16* sl = reinterpret_cast<const bf16*>(ring + slot * kSlotBytes);
-        if (along_k) mma_chunk<M16>(acc[0], As, ch, sl, warp, g, t4);
-        else if (ch == 0) mma_chunk<M16>(acc[0], As, 0, sl, warp, g, t4);
-        else mma_chunk<M16>(acc[1], As, 0, sl, warp, g, t4);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[slot]);
-        if (++slot == Cfg::kSlots) { slot = 0; phase ^= 1; }
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[b][a][e] = 0.0f;
+#pragma unroll
+      for (int b = 0; b < kUB; ++b) {
+        if (b < nb) {
+          for (int ch = 0; ch < nch; ++ch) {
+            mbar_wait(&full_bar[slot], phase);
+            const bf16* sl = reinterpret_cast<const bf16*>(ring + slot * kSlotBytes);
+            if (along_k) mma_chunk<M16>(acc[b][0], As, ch, sl, warp, g, t4);
+            else if (ch == 0) mma_chunk<M16>(acc[b][0], As, 0, sl, warp, g, t4);
+            else mma_chunk<M16>(acc[b][1], As, 0, sl, warp, g, t4);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[slot]);
+            if (++slot == Cfg::kSlots) { slot = 0; phase ^= 1; }
+          }
+        }
       }
-      float* rp = red + parity * (8 * 2 * 16 * 8);
+      // scratch layout [unit][warp][acc][row][col]
 #pragma unroll
-      for (int a = 0; a < 2; ++a) {
-        *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * 16 + g) * 8 + t4 * 2) = make_float2(acc[a][0], acc[a][1]);
-        *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * 16 + g + 8) * 8 + t4 * 2) = make_float2(acc[a][2], acc[a][3]);
+      for (int b = 0; b < kUB; ++b) {
+        if (b < nb) {
+          float* rp = red + b * (8 * 2 * kRowsR * 8);
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+            *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * kRowsR + g) * 8 + t4 * 2) = make_float2(acc[b][a][0], acc[b][a][1]);
+            if constexpr (M16)
+              *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * kRowsR + g + 8) * 8 + t4 * 2) =
+                  make_float2(acc[b][a][2], acc[b][a][3]);
+          }
+        }
       }
       consumer_sync();
-      if (threadIdx.x < 128) {
-        const int row = threadIdx.x >> 3, col = threadIdx.x & 7;
-        if (row < p.M) {
+      {
+        const int b = threadIdx.x / kEpiT, rem = threadIdx.x % kEpiT;
+        const int row = rem >> 3, col = rem & 7;
+        if (b < nb && row < p.M) {
+          const float* rp = red + b * (8 * 2 * kRowsR * 8);
           float t0 = 0.0f, t1 = 0.0f;
 #pragma unroll
           for (int w = 0; w < 8; ++w) {
-            t0 += rp[((w * 2 + 0) * 16 + row) * 8 + col];
-            t1 += rp[((w * 2 + 1) * 16 + row) * 8 + col];
+            t0 += rp[((w * 2 + 0) * kRowsR + row) * 8 + col];
+            t1 += rp[((w * 2 + 1) * kRowsR + row) * 8 + col];
           }
-          epi(u, row, col, t0, t1);
+          epi((int)t[1 + i0 + b], row, col, t0, t1);
         }
       }
-      parity ^= 1;
+      if (i0 + kUB < cnt) consumer_sync();  // the scratch is rewritten by the next batch
     }
   };
 
@@ -332,6 +361,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
 
     // ---- phase 1: q|k|v = RMSNorm(x) . Wqkv^T, RoPE, caches ------------------------------------------------------
     MEGA_STAMP(0);
+    prefetch_gain_l2(lw.g2);
     if (layer > 0) grid_barrier(gb);
     MEGA_STAMP(1);
     stage_norm<M16>(As, x_in, lw.g1, p.M);
@@ -419,6 +449,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
       p.x[(int64_t)row * kHidden + n] = to_bf16(v);
     });
     MEGA_STAMP(14);
+    if (layer + 1 < p.n_layers) prefetch_gain_l2(p.L[layer + 1].g1);
   }
 }
 

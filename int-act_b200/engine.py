@@ -127,7 +127,9 @@ class Pi0Engine:
             st["x_t"].copy_(keep)
             g = torch.cuda.CUDAGraph()
             self.lib.pi0_launch_count(1)
-            with torch.cuda.graph(g):
+            # torch.cuda.graph's default capture stream is created once per process on whatever device was current then:
+            # an engine on another GPU must bring its own, or the capture records nothing ("The CUDA Graph is empty")
+            with torch.cuda.graph(g, stream=side):
                 self._infer_raw(B, st["images"], st["img_masks"], st["tokens"], st["lang_masks"], st["state"], st["x_t"])
             self.launches_per_infer[B] = int(self.lib.pi0_launch_count(1))
             st["x_t"].copy_(keep)

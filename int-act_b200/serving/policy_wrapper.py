@@ -174,25 +174,34 @@ class LeRobotPolicyWrapper:
         self._require_model()
         if len(elements) == 1 or not self.can_batch():
             return [self.select_action(e) for e in elements]
-        pre, failed = [], {}
-        for i, e in enumerate(elements):
-            try:
-                pre.append((i, self.env_adapter.preprocess(e)))
-            except Exception as exc:  # noqa: BLE001 - reported to the one client that sent it
-                failed[i] = exc
+        pre, failed, batch = [], {}, None
+        if hasattr(self.env_adapter, "preprocess_many"):
+            try:  # one host concatenation + one H2D + one kernel for the whole group; any problem -> per-request path
+                sizes = [int(np.asarray(e["observation.state"]).reshape(-1, 8).shape[0]) for e in elements]
+                batch = self.env_adapter.preprocess_many(elements)
+                pre = [(i, None) for i in range(len(elements))]
+            except Exception:  # noqa: BLE001
+                batch, pre = None, []
+        if batch is None:
+            for i, e in enumerate(elements):
+                try:
+                    pre.append((i, self.env_adapter.preprocess(e)))
+                except Exception as exc:  # noqa: BLE001 - reported to the one client that sent it
+                    failed[i] = exc
         out: List[object] = [None] * len(elements)
         for i, exc in failed.items():
             out[i] = exc
         if not pre:
             return out
-        sizes = [p["observation.state"].shape[0] for _, p in pre]
-        batch = {}
-        for k in pre[0][1]:
-            vals = [p[k] for _, p in pre]
-            if isinstance(vals[0], torch.Tensor):
-                batch[k] = torch.cat(vals, dim=0)
-            else:
-                batch[k] = [t for v in vals for t in (v if isinstance(v, (list, tuple)) else [v])]
+        if batch is None:
+            sizes = [p["observation.state"].shape[0] for _, p in pre]
+            batch = {}
+            for k in pre[0][1]:
+                vals = [p[k] for _, p in pre]
+                if isinstance(vals[0], torch.Tensor):
+                    batch[k] = torch.cat(vals, dim=0)
+                else:
+                    batch[k] = [t for v in vals for t in (v if isinstance(v, (list, tuple)) else [v])]
         with torch.inference_mode():
             if hasattr(self.model, "reset"):
                 self.model.reset()

@@ -122,3 +122,60 @@ def test_checkpoint_hot_swap_through_the_server(cuda, tmp_path):
     assert a0.shape == (4, 7) and a0.dtype == np.float64
     assert np.array_equal(a0, a0b)                 # same checkpoint + same seed => same actions (deterministic path)
     assert np.abs(a0 - a1).max() > 1e-3            # the swapped-in weights are really in use
+
+
+def test_replicas_behind_one_port_on_the_gpu_and_worker_thread_device_pinning(cuda):
+    """Two engine replicas behind one websocket port (on two GPUs when the box has them, else both on cuda:0), driven from
+    the server's worker threads: exercises the per-device kernel attributes / device pinning (a worker thread's current
+    device is cuda:0 whatever device its engine lives on), request coalescing with pre-captured graphs and the latency
+    histogram. Every client must get the action of ITS observation whichever replica served it."""
+    from int_act_b200.serving import WebsocketPolicyClient, WebsocketPolicyServer
+
+    n_dev = torch.cuda.device_count()
+    devs = [torch.device("cuda", 0), torch.device("cuda", 1 if n_dev > 1 else 0)]
+    wrappers = []
+    for d in devs:
+        w, sd, dims, stats, tok = _build(d, max_batch=4)
+        w.env_adapter = type(w.env_adapter)(__import__("int_act_b200.adapters", fromlist=["x"]).adapter_config(
+            "unused", use_bf16=True), dataset_statistics=stats, device=d)
+        w.max_batch = 4
+        w.warmup(4)                      # graphs for batch 1..4 captured before the first request
+        assert sorted(w.model._engine._graphs) == [1, 2, 3, 4]
+        wrappers.append(w)
+    rng = np.random.default_rng(1)
+    n = 8
+    frames = rng.integers(0, 256, (n, 480, 640, 3), dtype=np.uint8)
+    eef = np.load(os.path.join(G, "adapter_batch.npz"))["eef"]
+    eef = np.concatenate([eef] * (n // len(eef) + 1))[:n].astype(np.float32)
+    noise = torch.normal(0.0, 1.0, (1, 4, 32), generator=torch.Generator().manual_seed(42))
+    for w in wrappers:   # same noise row for every observation -> the result depends only on the observation
+        eng = w.model._engine
+        orig = eng.sample_actions
+        eng.sample_actions = lambda *a, orig=orig, eng=eng, **k: orig(*a[:5], noise.to(eng.device).expand(a[4].shape[0], 4, 32))
+    single = [wrappers[0].select_action({"observation.images.top": frames[i:i + 1], "observation.state": eef[i:i + 1],
+                                         "task": ["put the carrot on the plate"]}) for i in range(n)]
+    srv_obj = ServerThread.__new__(ServerThread)
+    srv_obj.server = WebsocketPolicyServer(wrappers[0], host="127.0.0.1", port=0, metadata={}, max_batch=4,
+                                           batch_window_ms=20.0, replicas=wrappers[1:])
+    srv_obj.ready = threading.Event()
+    srv_obj.thread = threading.Thread(target=srv_obj._main, daemon=True)
+    with srv_obj as srv:
+        clients = [WebsocketPolicyClient("127.0.0.1", srv.bound_port) for _ in range(n)]
+        out = [None] * n
+
+        def run(i):
+            for _ in range(3):
+                out[i] = clients[i].infer({"observation.images.top": frames[i:i + 1], "observation.state": eef[i:i + 1],
+                                           "task": ["put the carrot on the plate"]})
+        ts = [threading.Thread(target=run, args=(i,)) for i in range(n)]
+        [t.start() for t in ts]
+        [t.join(120) for t in ts]
+        stats_srv, lat = dict(srv.stats), srv.latency_ms()
+        [c.close() for c in clients]
+    for i in range(n):
+        assert out[i] is not None and out[i].shape == single[i].shape
+        assert np.abs(out[i][..., :6] - single[i][..., :6]).max() <= 2e-2, i      # batch composition changes bf16 rounding paths
+    assert stats_srv["requests"] == 3 * n and stats_srv["failed_requests"] == 0
+    assert sum(1 for b in stats_srv["per_replica_batches"] if b > 0) == 2, stats_srv
+    assert lat["n"] == 3 * n and lat["p99"] >= lat["p50"] > 0
+    print(f"\n[2 replicas on {n_dev} GPU(s)] {stats_srv}; latency ms {lat}")
