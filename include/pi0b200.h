@@ -154,6 +154,11 @@ int pi0_profile_report(pi0_ctx* ctx, char* buf, size_t buf_bytes);
  * this call makes every such fallback visible. Host only, no launch. */
 int pi0_path_report(pi0_ctx* ctx, int B, char* buf, size_t buf_bytes);
 
+/* Bounds check of our own (compute-sanitizer is not available on the GPU pool): with PI0_GUARD=1 in the environment when
+ * pi0_workspace_bytes / pi0_ctx_create run, every workspace buffer is followed by a guard zone filled with 0xA5;
+ * this call synchronises the device and verifies the zones. 0 = intact, 1 = overwritten (description in buf), < 0 = error. */
+int pi0_debug_check_guards(pi0_ctx* ctx, char* buf, size_t buf_bytes);
+
 /* kernels launched by this library since the last call with reset != 0 (bench "gpu_launches") */
 long long pi0_launch_count(int reset);
 

@@ -93,6 +93,7 @@ SIGNATURES = {
     "pi0_profile": (C.c_int, [c_ptr, C.c_int]),
     "pi0_profile_report": (C.c_int, [c_ptr, C.c_char_p, C.c_size_t]),
     "pi0_path_report": (C.c_int, [c_ptr, C.c_int, C.c_char_p, C.c_size_t]),
+    "pi0_debug_check_guards": (C.c_int, [c_ptr, C.c_char_p, C.c_size_t]),
     "pi0_launch_count": (C.c_longlong, [C.c_int]),
     "pi0_gemm": (C.c_int, [C.POINTER(GemmDesc), C.c_int, C.c_int, C.c_int, c_ptr]),
     "pi0_rmsnorm": (C.c_int, [c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, c_ptr]),

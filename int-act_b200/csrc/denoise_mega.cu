@@ -46,14 +46,22 @@ __device__ unsigned long long g_mega_tl[4][32];
 #define MEGA_STAMP(i) do { } while (0)
 #endif
 
-template <bool M16>
+// R = rows of the staged activation operand: 8 (M <= 8: half an MMA tile), 16, or 32 / 48 (two / three m16 tiles, batch 4-9
+// at the bridge shapes). Up to 16 rows the operand is staged for the whole K (up to 4096) at once; above that it would not
+// fit next to the weight ring, so it is staged one 1024-k chunk at a time and the along-K phases (o_proj, down) re-stage
+// between the chunks of their unit.
+template <int R>
 struct MegaCfg {
-  static constexpr int kRows = M16 ? 16 : 8;
-  static constexpr int kSlots = M16 ? 4 : 8;
+  static constexpr int kRows = R;
+  static constexpr bool kChunkedA = R > 16;
+  static constexpr int kPitch = kChunkedA ? kChunkK + 32 : kAPitch;  // bf16 elements per staged row (64 mod 128 bytes)
+  static constexpr int kMT = R <= 16 ? 1 : R / 16;                   // m16 tiles
+  static constexpr int kSlots = R == 8 ? 8 : R == 16 ? 4 : R == 32 ? 8 : 6;
   static constexpr int kRingBytes = kSlots * kSlotBytes;
-  static constexpr int kABytes = kRows * kAPitch * 2;
-  static constexpr int kRedBytes = 2 * 8 * 2 * 16 * 8 * 4;  // [parity][warp][acc][row][col] fp32
+  static constexpr int kABytes = kRows * kPitch * 2;
+  static constexpr int kRedBytes = R <= 16 ? 2 * 8 * 2 * 16 * 8 * 4 : 8 * 2 * R * 8 * 4;  // [unit][warp][acc][row][col] fp32
   static constexpr int kSmem = kRingBytes + kABytes + kRedBytes + 256 + 128;
+  static_assert(kSmem <= 232448, "shared memory budget of one SM");
 };
 
 __device__ __forceinline__ uint64_t policy_evict_first() {
@@ -134,27 +142,32 @@ struct RingState {
   uint32_t phase;
 };
 
-template <bool M16>
+template <int R>
 __device__ __forceinline__ void mma_chunk(float* acc, const bf16* As, int kc, const bf16* slot, int warp, int g,
                                           int t4) {
-  const int k0 = warp * 128 + t4 * 8;
+  using Cfg = MegaCfg<R>;
+  const int k0 = warp * 128 + t4 * 8 + (Cfg::kChunkedA ? 0 : kc * kChunkK);
+  const int w0 = warp * 128 + t4 * 8;
 #pragma unroll
   for (int cc = 0; cc < 4; ++cc) {
-    const uint4 w = *reinterpret_cast<const uint4*>(slot + g * kRowPitch + k0 + cc * 32);
-    const uint4 lo = *reinterpret_cast<const uint4*>(As + g * kAPitch + kc * kChunkK + k0 + cc * 32);
-    uint4 hi = make_uint4(0, 0, 0, 0);
-    if constexpr (M16) hi = *reinterpret_cast<const uint4*>(As + (g + 8) * kAPitch + kc * kChunkK + k0 + cc * 32);
-    mma_bf16_16816(acc, lo.x, hi.x, lo.y, hi.y, w.x, w.y);
-    mma_bf16_16816(acc, lo.z, hi.z, lo.w, hi.w, w.z, w.w);
+    const uint4 w = *reinterpret_cast<const uint4*>(slot + g * kRowPitch + w0 + cc * 32);
+#pragma unroll
+    for (int mt = 0; mt < Cfg::kMT; ++mt) {
+      const uint4 lo = *reinterpret_cast<const uint4*>(As + (g + 16 * mt) * Cfg::kPitch + k0 + cc * 32);
+      uint4 hi = make_uint4(0, 0, 0, 0);
+      if constexpr (R >= 16) hi = *reinterpret_cast<const uint4*>(As + (g + 8 + 16 * mt) * Cfg::kPitch + k0 + cc * 32);
+      mma_bf16_16816(acc + 4 * mt, lo.x, hi.x, lo.y, hi.y, w.x, w.y);
+      mma_bf16_16816(acc + 4 * mt, lo.z, hi.z, lo.w, hi.w, w.z, w.w);
+    }
   }
 }
 
 // A = rnd((x * rsqrt(mean(x^2) + eps)) * (1 + w)) for M rows of 1024 -> shared memory. Warp w normalises rows w, w + 8.
-template <bool M16>
+template <int R>
 __device__ __forceinline__ void stage_norm(bf16* As, const bf16* x, const float* gain, int M) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-  for (int rr = 0; rr < (M16 ? 2 : 1); ++rr) {
+#pragma unroll 1
+  for (int rr = 0; rr < R / 8; ++rr) {
     const int row = warp + rr * 8;
     if (row >= M) continue;
     uint4 v[4];
@@ -186,13 +199,14 @@ __device__ __forceinline__ void stage_norm(bf16* As, const bf16* x, const float*
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         oh[j] = __floats2bfloat162_rn((f[i][2 * j] * r) * gv[2 * j], (f[i][2 * j + 1] * r) * gv[2 * j + 1]);
-      *reinterpret_cast<uint4*>(As + row * kAPitch + k) = o;
+      *reinterpret_cast<uint4*>(As + row * MegaCfg<R>::kPitch + k) = o;
     }
   }
 }
 
-// plain copy of M rows x K (K multiple of 8) into the staged operand; 8 independent 16-byte loads in flight per thread
-__device__ __forceinline__ void stage_copy(bf16* As, const bf16* src, int ld, int M, int K) {
+// plain copy of M rows x K (K multiple of 8) starting at column `kofs` of `src` into the staged operand (row pitch `pitch`
+// elements); 8 independent 16-byte loads in flight per thread
+__device__ __forceinline__ void stage_copy(bf16* As, int pitch, const bf16* src, int ld, int M, int K, int kofs) {
   const int per_row = K >> 3;
   const int total = M * per_row;
   for (int i0 = threadIdx.x; i0 < total; i0 += 256 * 8) {
@@ -202,7 +216,7 @@ __device__ __forceinline__ void stage_copy(bf16* As, const bf16* src, int ld, in
       const int i = i0 + j * 256;
       if (i < total) {
         const int row = i / per_row, c8 = i - row * per_row;
-        v[j] = ldcg_u4(src + (int64_t)row * ld + c8 * 8);
+        v[j] = ldcg_u4(src + (int64_t)row * ld + kofs + c8 * 8);
       }
     }
 #pragma unroll
@@ -210,15 +224,15 @@ __device__ __forceinline__ void stage_copy(bf16* As, const bf16* src, int ld, in
       const int i = i0 + j * 256;
       if (i < total) {
         const int row = i / per_row, c8 = i - row * per_row;
-        *reinterpret_cast<uint4*>(As + row * kAPitch + c8 * 8) = v[j];
+        *reinterpret_cast<uint4*>(As + row * pitch + c8 * 8) = v[j];
       }
     }
   }
 }
 
-template <bool M16>
+template <int R>
 __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaParams p) {
-  using Cfg = MegaCfg<M16>;
+  using Cfg = MegaCfg<R>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   uint8_t* ring = smem;
@@ -288,32 +302,40 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
   // (round 1 paid a reduction, a barrier and a 128-thread epilogue per unit: ~1.2 us each on the critical path, 4 units in
   // the gate/up phase). `epi(u, row, col, t0, t1)` is called with row < M; the fp32 sum over the 8 warps keeps its fixed
   // order, so results are bit-identical to the per-unit form.
-  constexpr int kUB = M16 ? 2 : 4;           // units per batch
-  constexpr int kRowsR = M16 ? 16 : 8;       // rows kept in the reduction scratch
-  constexpr int kEpiT = kRowsR * 8;          // epilogue threads per unit
-  auto run_units = [&](int ph, auto&& epi) {
+  constexpr int kUB = R == 8 ? 4 : R == 16 ? 2 : 1;   // units per batch
+  constexpr int kEpiT = R * 8;                        // epilogue (row, col) pairs per unit
+  constexpr int kAccN = 4 * Cfg::kMT;
+  // `a_src` / `a_ld`: the activation source of an along-K phase, needed only when the operand is staged chunk by chunk
+  auto run_units = [&](int ph, const bf16* a_src, int a_ld, auto&& epi) {
     const int nch = ph == MEGA_DOWN ? 4 : 2;
     const bool along_k = ph == MEGA_O || ph == MEGA_DOWN;
     const int16_t* t = tab + ph * (kMegaMaxUnits + 1);
     const int cnt = t[0];
     for (int i0 = 0; i0 < cnt; i0 += kUB) {
       const int nb = min(kUB, cnt - i0);
-      float acc[kUB][2][4];
+      float acc[kUB][2][kAccN];
 #pragma unroll
       for (int b = 0; b < kUB; ++b)
 #pragma unroll
         for (int a = 0; a < 2; ++a)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) acc[b][a][e] = 0.0f;
+          for (int e = 0; e < kAccN; ++e) acc[b][a][e] = 0.0f;
 #pragma unroll
       for (int b = 0; b < kUB; ++b) {
         if (b < nb) {
           for (int ch = 0; ch < nch; ++ch) {
+            if constexpr (Cfg::kChunkedA) {
+              if (along_k && (ch > 0 || i0 > 0)) {  // next 1024-k slice of the activations (slice 0 was staged by the caller)
+                consumer_sync();
+                stage_copy(As, Cfg::kPitch, a_src, a_ld, p.M, kChunkK, ch * kChunkK);
+                consumer_sync();
+              }
+            }
             mbar_wait(&full_bar[slot], phase);
             const bf16* sl = reinterpret_cast<const bf16*>(ring + slot * kSlotBytes);
-            if (along_k) mma_chunk<M16>(acc[b][0], As, ch, sl, warp, g, t4);
-            else if (ch == 0) mma_chunk<M16>(acc[b][0], As, 0, sl, warp, g, t4);
-            else mma_chunk<M16>(acc[b][1], As, 0, sl, warp, g, t4);
+            if (along_k) mma_chunk<R>(acc[b][0], As, ch, sl, warp, g, t4);
+            else if (ch == 0) mma_chunk<R>(acc[b][0], As, 0, sl, warp, g, t4);
+            else mma_chunk<R>(acc[b][1], As, 0, sl, warp, g, t4);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[slot]);
             if (++slot == Cfg::kSlots) { slot = 0; phase ^= 1; }
@@ -324,27 +346,31 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
 #pragma unroll
       for (int b = 0; b < kUB; ++b) {
         if (b < nb) {
-          float* rp = red + b * (8 * 2 * kRowsR * 8);
+          float* rp = red + b * (8 * 2 * R * 8);
 #pragma unroll
           for (int a = 0; a < 2; ++a) {
-            *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * kRowsR + g) * 8 + t4 * 2) = make_float2(acc[b][a][0], acc[b][a][1]);
-            if constexpr (M16)
-              *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * kRowsR + g + 8) * 8 + t4 * 2) =
-                  make_float2(acc[b][a][2], acc[b][a][3]);
+#pragma unroll
+            for (int mt = 0; mt < Cfg::kMT; ++mt) {
+              *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * R + g + 16 * mt) * 8 + t4 * 2) =
+                  make_float2(acc[b][a][4 * mt + 0], acc[b][a][4 * mt + 1]);
+              if constexpr (R >= 16)
+                *reinterpret_cast<float2*>(rp + ((warp * 2 + a) * R + g + 8 + 16 * mt) * 8 + t4 * 2) =
+                    make_float2(acc[b][a][4 * mt + 2], acc[b][a][4 * mt + 3]);
+            }
           }
         }
       }
       consumer_sync();
-      {
-        const int b = threadIdx.x / kEpiT, rem = threadIdx.x % kEpiT;
+      for (int e = threadIdx.x; e < kUB * kEpiT; e += 256) {
+        const int b = e / kEpiT, rem = e % kEpiT;
         const int row = rem >> 3, col = rem & 7;
         if (b < nb && row < p.M) {
-          const float* rp = red + b * (8 * 2 * kRowsR * 8);
+          const float* rp = red + b * (8 * 2 * R * 8);
           float t0 = 0.0f, t1 = 0.0f;
 #pragma unroll
           for (int w = 0; w < 8; ++w) {
-            t0 += rp[((w * 2 + 0) * kRowsR + row) * 8 + col];
-            t1 += rp[((w * 2 + 1) * kRowsR + row) * 8 + col];
+            t0 += rp[((w * 2 + 0) * R + row) * 8 + col];
+            t1 += rp[((w * 2 + 1) * R + row) * 8 + col];
           }
           epi((int)t[1 + i0 + b], row, col, t0, t1);
         }
@@ -352,6 +378,7 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
       if (i0 + kUB < cnt) consumer_sync();  // the scratch is rewritten by the next batch
     }
   };
+  auto has_units = [&](int ph) -> bool { return tab[ph * (kMegaMaxUnits + 1)] > 0; };
 
   for (int layer = 0; layer < p.n_layers; ++layer) {
     const MegaLayerW& lw = p.L[layer];
@@ -364,10 +391,10 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
     prefetch_gain_l2(lw.g2);
     if (layer > 0) grid_barrier(gb);
     MEGA_STAMP(1);
-    stage_norm<M16>(As, x_in, lw.g1, p.M);
+    stage_norm<R>(As, x_in, lw.g1, p.M);
     consumer_sync();
     MEGA_STAMP(2);
-    run_units(MEGA_QKV, [&](int u, int row, int col, float t0, float t1) {
+    run_units(MEGA_QKV, nullptr, 0, [&](int u, int row, int col, float t0, float t1) {
       const int head = u >> 4, d = (u & 15) * 8 + col;
       const float a = bf16_round(t0), b = bf16_round(t1);
       float o1 = a, o2 = b;
@@ -412,10 +439,10 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
     MEGA_STAMP(5);
     grid_barrier(gb);
     MEGA_STAMP(6);
-    stage_copy(As, p.att, kQDim, p.M, kQDim);
+    if (has_units(MEGA_O)) stage_copy(As, Cfg::kPitch, p.att, kQDim, p.M, Cfg::kChunkedA ? kChunkK : kQDim, 0);
     consumer_sync();
     MEGA_STAMP(7);
-    run_units(MEGA_O, [&](int u, int row, int col, float t0, float) {
+    run_units(MEGA_O, p.att, kQDim, [&](int u, int row, int col, float t0, float) {
       const int n = u * 8 + col;
       const unsigned short xb = __ldcg(reinterpret_cast<const unsigned short*>(x_in) + (int64_t)row * kHidden + n);
       const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(xb));
@@ -426,10 +453,10 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
     MEGA_STAMP(8);
     grid_barrier(gb);
     MEGA_STAMP(9);
-    stage_norm<M16>(As, p.y, lw.g2, p.M);
+    stage_norm<R>(As, p.y, lw.g2, p.M);
     consumer_sync();
     MEGA_STAMP(10);
-    run_units(MEGA_GU, [&](int u, int row, int col, float t0, float t1) {
+    run_units(MEGA_GU, nullptr, 0, [&](int u, int row, int col, float t0, float t1) {
       const float gt = bf16_round(t0), up = bf16_round(t1);
       const float act = bf16_round(gelu_tanh_fast(gt));
       p.act[(int64_t)row * kInter + u * 8 + col] = to_bf16(act * up);
@@ -439,10 +466,10 @@ __global__ void __launch_bounds__(kThreads, 1) denoise_layers_kernel(const MegaP
     MEGA_STAMP(11);
     grid_barrier(gb);
     MEGA_STAMP(12);
-    stage_copy(As, p.act, kInter, p.M, kInter);
+    if (has_units(MEGA_DOWN)) stage_copy(As, Cfg::kPitch, p.act, kInter, p.M, Cfg::kChunkedA ? kChunkK : kInter, 0);
     consumer_sync();
     MEGA_STAMP(13);
-    run_units(MEGA_DOWN, [&](int u, int row, int col, float t0, float) {
+    run_units(MEGA_DOWN, p.act, kInter, [&](int u, int row, int col, float t0, float) {
       const int n = u * 8 + col;
       const unsigned short yb = __ldcg(reinterpret_cast<const unsigned short*>(p.y) + (int64_t)row * kHidden + n);
       const float v = bf16_round(t0) + __bfloat162float(__ushort_as_bfloat16(yb));
@@ -478,22 +505,23 @@ int mega_build_units(int G, std::vector<int16_t>& tab) {
   return 0;
 }
 
-bool mega_supported(int M, int S, int P) { return M >= 1 && M <= 16 && S <= 16 && P + S <= 32 * kMegaKeyChunks; }
+bool mega_supported(int M, int S, int P) { return M >= 1 && M <= 48 && S <= 16 && P + S <= 32 * kMegaKeyChunks; }
 
 int mega_denoise_layers(const MegaParams& p, int num_ctas, cudaStream_t s) {
   PI0_REQUIRE(mega_supported(p.M, p.S, p.P), "denoise mega kernel: M=%d S=%d P=%d unsupported", p.M, p.S, p.P);
   PI0_REQUIRE(p.n_layers >= 1 && p.n_layers <= 18, "denoise mega kernel: n_layers=%d", p.n_layers);
-  const bool m16 = p.M > 8;
-  const size_t smem = m16 ? MegaCfg<true>::kSmem : MegaCfg<false>::kSmem;
-  PI0_REQUIRE(16 * attn_p_pitch_bytes(p.kp) <= (m16 ? MegaCfg<true>::kABytes : MegaCfg<false>::kABytes) && p.kp <= 32 * kMegaKeyChunks &&
-                  p.kp % 32 == 0 && p.sc != nullptr,
+  const int R = p.M <= 8 ? 8 : p.M <= 16 ? 16 : p.M <= 32 ? 32 : 48;
+  const size_t smem = R == 8 ? MegaCfg<8>::kSmem : R == 16 ? MegaCfg<16>::kSmem : R == 32 ? MegaCfg<32>::kSmem : MegaCfg<48>::kSmem;
+  const size_t abytes = R == 8 ? MegaCfg<8>::kABytes : R == 16 ? MegaCfg<16>::kABytes : R == 32 ? MegaCfg<32>::kABytes
+                                                                                                : MegaCfg<48>::kABytes;
+  PI0_REQUIRE((size_t)16 * attn_p_pitch_bytes(p.kp) <= abytes && p.kp <= 32 * kMegaKeyChunks && p.kp % 32 == 0 && p.sc != nullptr,
               "denoise mega kernel: attention scratch does not fit");
   static PerDeviceOnce attr_once;
   if (attr_once.need()) {
-    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)MegaCfg<true>::kSmem));
-    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)MegaCfg<false>::kSmem));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MegaCfg<8>::kSmem));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MegaCfg<16>::kSmem));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MegaCfg<32>::kSmem));
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(denoise_layers_kernel<48>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MegaCfg<48>::kSmem));
     attr_once.mark();
   }
   cudaLaunchConfig_t lc = {};
@@ -506,8 +534,10 @@ int mega_denoise_layers(const MegaParams& p, int num_ctas, cudaStream_t s) {
   at[0].val.cooperative = 1;
   lc.attrs = at;
   lc.numAttrs = 1;
-  if (m16) PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<true>, p));
-  else PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<false>, p));
+  if (R == 8) PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<8>, p));
+  else if (R == 16) PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<16>, p));
+  else if (R == 32) PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<32>, p));
+  else PI0_CHECK_CUDA(cudaLaunchKernelEx(&lc, denoise_layers_kernel<48>, p));
   ++g_launch_count;
   return 0;
 }

@@ -65,6 +65,7 @@ struct pi0_ctx {
   unsigned* mega_sync;
   void* mega_sc;
   int mega_ctas;  // 0 = unavailable / disabled (PI0_MEGA=0)
+  int mega_max_rows;  // largest M = B * S the persistent per-step kernel takes (PI0_MEGA_MAX_ROWS, default 32)
   // whole-loop persistent denoise kernel (denoise_loop.cu): unit table, flag-in-data exchange arena and its epoch word
   int16_t* loop_units;
   uint4* loop_ll;
@@ -77,6 +78,7 @@ struct pi0_ctx {
   int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
   Buf bufs[48];
   int nbufs;
+  bool guarded;  // PI0_GUARD: 1 KiB 0xA5 zones behind every buffer
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
   bool prof_on;
   struct ProfRec { const char* label; cudaEvent_t e0, e1; };
@@ -100,13 +102,24 @@ struct ProfScope {
 #define PROF(label) ProfScope _prof_scope(c, label, s)
 
 // ---- workspace carving (shared by pi0_workspace_bytes and pi0_ctx_create) ------------------------------
+// PI0_GUARD=1 (development / tests): every workspace buffer is followed by a 1 KiB guard zone filled with 0xA5 at ctx
+// creation; pi0_debug_check_guards verifies them after a run. compute-sanitizer is closed on this GPU pool, so this is the
+// bounds check of our own: any kernel writing past the end of its buffer (or before the start of the next) trips it.
+constexpr size_t kGuardBytes = 1024;
+inline bool guard_enabled() {
+  const char* e = getenv("PI0_GUARD");
+  return e && strcmp(e, "0") != 0;
+}
+
 struct Carver {
   size_t off = 0;
   uint8_t* base = nullptr;
   pi0_ctx* ctx = nullptr;
+  bool guard = guard_enabled();
   void* take(const char* name, size_t bytes) {
     size_t o = off;
     off = round_up((int64_t)(off + bytes), 1024);
+    if (guard) off += kGuardBytes;
     if (ctx && ctx->nbufs < 48) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
     return base ? base + o : nullptr;
   }
@@ -174,7 +187,7 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.suffix_cum = (int*)cv.take("suffix_cum", S * 4);
   x.mega_units = (int16_t*)cv.take("mega.units", (size_t)1024 * 4 * (kMegaMaxUnits + 1) * 2);
   x.mega_sync = (unsigned*)cv.take("mega.sync", 64);
-  x.mega_sc = cv.take("mega.scores", (size_t)16 * 8 * 640 * 2);
+  x.mega_sc = cv.take("mega.scores", (size_t)48 * 8 * 640 * 2);
   x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
   x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
   x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
@@ -406,6 +419,15 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   cv.base = c->base;
   cv.ctx = c;
   carve(cv, c, *cfg);
+  c->guarded = cv.guard;
+  if (c->guarded) {
+    for (int i = 0; i < c->nbufs; ++i) {
+      const size_t g0 = (size_t)round_up((int64_t)(c->bufs[i].offset + c->bufs[i].bytes), 1024);
+      // the slack between the end of the buffer and the 1 KiB boundary belongs to the guard as well
+      PI0_CHECK_CUDA(cudaMemset(c->base + c->bufs[i].offset + c->bufs[i].bytes, 0xA5,
+                                g0 + kGuardBytes - (c->bufs[i].offset + c->bufs[i].bytes)));
+    }
+  }
   // persistent denoise kernel: deal the work units to one CTA per SM (bf16 product path only)
   c->mega_ctas = 0;
   {
@@ -425,6 +447,9 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   const int mega_sel = mega_env ? atoi(mega_env) : 1;
   const int sms = cfg->num_sms > 0 ? cfg->num_sms : 148;
   c->loop_mode = 0;
+  // measured in graph replay (full depth): batch 4 / 5 / 6 = 16.2 / 18.9 / 19.8 ms with the persistent kernel against 18.7 /
+  // 19.8 / 20.7 ms per op, but 22.9 against 21.2 ms at batch 7 (three m16 tiles, five ring slots): it stops at 32 rows
+  c->mega_max_rows = getenv("PI0_MEGA_MAX_ROWS") ? atoi(getenv("PI0_MEGA_MAX_ROWS")) : 32;
   c->loop_pace_ns = getenv("PI0_LOOP_PACE") ? atoi(getenv("PI0_LOOP_PACE")) : 0;
   if (cfg->dtype == 0 && cfg->gemm_impl == 0 && mega_sel != 0 && sms >= 64 && sms <= 1024) {
     std::vector<int16_t> tab;
@@ -490,6 +515,30 @@ int pi0_profile_report(pi0_ctx* c, char* buf, size_t buf_bytes) {
   return 0;
 }
 
+int pi0_debug_check_guards(pi0_ctx* c, char* buf, size_t buf_bytes) {
+  // Returns 0 when every guard zone still holds its pattern, 1 when one was overwritten (its buffer's name and the first bad
+  // byte offset go to `buf`), < 0 on errors (guards not enabled: PI0_GUARD=1 before pi0_workspace_bytes / pi0_ctx_create).
+  PI0_REQUIRE(c != nullptr && buf != nullptr && buf_bytes > 0, "pi0_debug_check_guards: bad arguments");
+  PI0_REQUIRE(c->guarded, "pi0_debug_check_guards: the ctx was created without PI0_GUARD=1");
+  buf[0] = 0;
+  PI0_CHECK_CUDA(cudaDeviceSynchronize());
+  std::vector<uint8_t> host(2 * kGuardBytes);
+  for (int i = 0; i < c->nbufs; ++i) {
+    const size_t end = c->bufs[i].offset + c->bufs[i].bytes;
+    const size_t g1 = (size_t)round_up((int64_t)end, 1024) + kGuardBytes;
+    const size_t n = g1 - end;
+    PI0_CHECK_CUDA(cudaMemcpy(host.data(), c->base + end, n, cudaMemcpyDeviceToHost));
+    for (size_t j = 0; j < n; ++j) {
+      if (host[j] != 0xA5) {
+        snprintf(buf, buf_bytes, "guard behind '%s' overwritten at +%zu bytes past its end (value 0x%02x)", c->bufs[i].name,
+                 j, (unsigned)host[j]);
+        return 1;
+      }
+    }
+  }
+  return 0;
+}
+
 int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
   // Which kernel variant every phase of pi0_infer takes at batch B with this ctx: the same predicates as gemma_layer /
   // pi0_siglip_forward / pi0_denoise_loop, so that silent fallbacks (P > 336, P + S > 352, S > 16, fp32 ...) are visible.
@@ -508,7 +557,7 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
   if (c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(M, S, P, c->mega_ctas)) {
     denoise = c->loop_mode == 2 ? "loop_kernel_whole_euler_loop" : "loop_kernel_per_step";
     denoise_attn = "in_kernel";
-  } else if (c->mega_ctas > 0 && mega_supported(M, S, P)) {
+  } else if (c->mega_ctas > 0 && M <= c->mega_max_rows && mega_supported(M, S, P)) {
     denoise = "persistent_layers_kernel_per_step";
     denoise_attn = "in_kernel";
   } else if (bf && skinny_supported(M) && S <= 48 && P + S <= 640) {
@@ -773,7 +822,7 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
       lp.n_steps = 1;
       lp.layers_only = 1;
       PI0_TRY(loop_denoise(lp, c->mega_ctas, s));
-    } else if (c->mega_ctas > 0 && mega_supported(B * S, S, c->P)) {
+    } else if (c->mega_ctas > 0 && B * S <= c->mega_max_rows && mega_supported(B * S, S, c->P)) {
       // latency regime: all expert layers of this step in one persistent cooperative launch
       PROF("denoise.layers_mega");
       MegaParams mp = {};

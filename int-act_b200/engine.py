@@ -206,6 +206,16 @@ class Pi0Engine:
         pb.check(self.lib.pi0_path_report(self.ctx, B, buf, len(buf)), "pi0_path_report")
         return json.loads(buf.value.decode())
 
+    def check_guards(self) -> None:
+        """With PI0_GUARD=1 set before the engine was built: raises if any kernel wrote past the end of a workspace buffer."""
+        buf = C.create_string_buffer(512)
+        with torch.cuda.device(self.device):
+            rc = self.lib.pi0_debug_check_guards(self.ctx, buf, len(buf))
+        if rc < 0:
+            pb.check(rc, "pi0_debug_check_guards")
+        if rc != 0:
+            raise pb.Pi0Error(f"workspace guard violated: {buf.value.decode()}")
+
     def debug_buffer(self, name: str, dtype=None) -> torch.Tensor:
         """Copy of a named workspace buffer (parity tests)."""
         n = C.c_int64()

@@ -83,3 +83,30 @@ def test_graph_replays_advance_the_epoch_and_stay_deterministic(cuda):
     assert eng.launches_per_infer[1] <= eager.launches_per_infer[1] - 60
     epoch = eng.debug_buffer("loop.epoch", dtype=torch.int32)[0].item()
     assert epoch > 0
+
+
+@pytest.mark.parametrize("B,n_valid", [(4, [72, 9, 33, 2]), (6, [72, 9, 33, 2, 50, 17]), (9, [5, 30, 72, 64, 1, 12, 40, 72, 9])])
+def test_persistent_kernel_with_chunked_operand_staging_for_batch_4_to_9(cuda, B, n_valid):
+    """M = 5 B suffix rows in (16, 48]: the persistent per-step kernel runs two / three m16 tiles with the activation operand
+    staged one 1024-k slice at a time (round 1 fell back to ~90 per-op launches per step from batch 4 on). Checked against
+    the per-op launches and the oracle."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=3, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=5)
+    packed = PackedWeights(sd, cuda, torch.bfloat16)
+    inp = synthetic_inputs(B, vocab=dims.vocab, n_valid_text=n_valid)
+    args = _args(cuda, inp)
+    os.environ["PI0_MEGA_MAX_ROWS"] = "48"     # the default stops at 32 rows (batch 6): 48 rows measured slower than per-op
+    try:
+        e_mega = _engine(packed, B, 1)
+    finally:
+        os.environ.pop("PI0_MEGA_MAX_ROWS", None)
+    assert e_mega.path_report(B)["denoise"] == "persistent_layers_kernel_per_step"
+    mega = e_mega.sample_actions(*args)
+    per_op = _engine(packed, B, 0).sample_actions(*args)
+    torch.cuda.synchronize()
+    ref = oracle_for(sd, dims, 1, 72, 4, "bf16").sample_actions(*inp)
+    err = (mega.cpu() - ref).abs().max().item()
+    dif = (mega - per_op).abs().max().item()
+    print(f"\n[persistent kernel B={B}] vs oracle {err:.3e}; vs per-op launches {dif:.3e}")
+    assert err <= 1e-2, err
+    assert dif <= 1e-2, dif

@@ -173,3 +173,28 @@ def test_path_report_names_the_variant_every_phase_takes(cuda):
     assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "gemm_softmax_gemm"
     f32 = Pi0Engine(PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.float32), dtype="fp32")
     assert f32.path_report(1)["gemm"] == "simt_fp32_check"
+
+
+@pytest.mark.parametrize("B,n_cams,horizon,mega", [(1, 1, 4, 1), (1, 1, 4, 3), (3, 1, 4, 1), (6, 1, 4, 1), (16, 1, 4, 1),
+                                                     (2, 2, 16, 1), (64, 1, 4, 1)])
+def test_no_kernel_writes_outside_its_workspace_buffer(cuda, monkeypatch, B, n_cams, horizon, mega):
+    """Bounds check of our own (compute-sanitizer is closed on this GPU pool, profiles/r02_sanitizer_summary.txt): with
+    PI0_GUARD=1 every workspace buffer is followed by a 0xA5 guard zone; after a full pi0_infer through each kernel family
+    (persistent denoise kernel, whole-loop kernel, split / batch decode attention, fused prefix attention, CTA-pair and
+    split-K GEMMs, LIBERO shapes) all zones must be intact - and a deliberate overrun must be caught."""
+    monkeypatch.setenv("PI0_GUARD", "1")
+    monkeypatch.setenv("PI0_MEGA", str(mega))
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=512)
+    sd = random_state_dict(dims, device=cuda, seed=0)
+    inp = synthetic_inputs(B, n_cams, 72, horizon, dims.vocab, [72, 9, 33])
+    eng, out = _engine_out(cuda, sd, "bf16", B, inp, n_cams, 72, horizon, graph=False)
+    assert torch.isfinite(out).all()
+    eng.check_guards()
+    if B == 1 and mega == 1:   # the check has teeth: write one byte past the end of a buffer
+        import ctypes as C
+        n = C.c_int64()
+        p = eng.lib.pi0_debug_buffer(eng.ctx, b"suffix.q", C.byref(n))
+        off = p - eng.workspace.data_ptr()
+        eng.workspace[off + n.value * 2] = 7
+        with pytest.raises(Exception, match="suffix.q"):
+            eng.check_guards()
