@@ -18,6 +18,7 @@
 
 #include "../../include/pi0b200.h"
 #include "denoise_loop.cuh"
+#include "fused_denoise.cuh"
 #include "denoise_mega.cuh"
 #include "elementwise.cuh"
 
@@ -70,6 +71,12 @@ struct pi0_ctx {
   int16_t* loop_units;
   uint4* loop_ll;
   unsigned* loop_epoch;
+  // fused denoise-step kernel for rollout batches (fused_denoise.cu): GEMM descriptors, split-K scratch, barrier counter
+  FusedGemmDesc* fused_descs;
+  float* fused_partial;
+  unsigned* fused_sync;
+  bool fused_on;  // PI0_FUSED=1 enables (opt-in: measured slower than the per-op launches)
+  int fused_min_batch;  // PI0_FUSED_MIN_BATCH (default 7)
   int loop_pace_ns;  // PI0_LOOP_PACE (development knob)
   int loop_mode;  // 0 = off, 1 = per-step layers-only launches (PI0_MEGA=2), 2 = the whole Euler loop in one launch (default)
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
@@ -188,6 +195,9 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.mega_units = (int16_t*)cv.take("mega.units", (size_t)1024 * 4 * (kMegaMaxUnits + 1) * 2);
   x.mega_sync = (unsigned*)cv.take("mega.sync", 64);
   x.mega_sc = cv.take("mega.scores", (size_t)48 * 8 * 640 * 2);
+  x.fused_descs = (FusedGemmDesc*)cv.take("fused.descs", fused_desc_bytes());
+  x.fused_partial = (float*)cv.take("fused.partial", fused_partial_bytes((int)Me, cfg.num_sms > 0 ? cfg.num_sms : 148));
+  x.fused_sync = (unsigned*)cv.take("fused.sync", 64);
   x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
   x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
   x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
@@ -469,6 +479,25 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
       cudaGetLastError();
     }
   }
+  c->fused_on = false;
+  c->fused_min_batch = getenv("PI0_FUSED_MIN_BATCH") ? atoi(getenv("PI0_FUSED_MIN_BATCH")) : 7;
+  {
+    const char* fe = getenv("PI0_FUSED");
+    if (cfg->dtype == 0 && cfg->gemm_impl == 0 && fe && strcmp(fe, "1") == 0) {
+      std::vector<FusedGemmDesc> descs;
+      const void* wq[18]; const void* wo[18]; const void* wg[18]; const void* wd[18];
+      for (int l = 0; l < cfg->n_gemma_layers; ++l) {
+        wq[l] = w->exp[l].wqkv; wo[l] = w->exp[l].wo; wg[l] = w->exp[l].wgu; wd[l] = w->exp[l].wdown;
+      }
+      if (fused_build_descs(descs, cfg->n_gemma_layers, c->maxB * c->S, c->he, c->att_e, c->act_e, wq, wo, wg, wd) == 0 &&
+          cudaMemcpy(c->fused_descs, descs.data(), descs.size() * sizeof(FusedGemmDesc), cudaMemcpyHostToDevice) == cudaSuccess &&
+          cudaMemset(c->fused_sync, 0, 64) == cudaSuccess) {
+        c->fused_on = true;
+      } else {
+        cudaGetLastError();
+      }
+    }
+  }
   *out = c;
   return 0;
 }
@@ -559,6 +588,9 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
     denoise_attn = "in_kernel";
   } else if (c->mega_ctas > 0 && M <= c->mega_max_rows && mega_supported(M, S, P)) {
     denoise = "persistent_layers_kernel_per_step";
+    denoise_attn = "in_kernel";
+  } else if (c->fused_on && M > c->mega_max_rows && B >= c->fused_min_batch && fused_supported(M, S, P, B, sms)) {
+    denoise = "fused_tcgen05_layers_kernel_per_step";
     denoise_attn = "in_kernel";
   } else if (bf && skinny_supported(M) && S <= 48 && P + S <= 640) {
     denoise = "skinny_mma_sync_per_op";
@@ -746,6 +778,9 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
   const float dt = -1.0f / (float)c->cfg.num_steps;
 
   const bool use_loop = c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(B * S, S, c->P, c->mega_ctas);
+  const int sms_n = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
+  const bool use_fused = c->fused_on && !use_loop && B * S > c->mega_max_rows && B >= c->fused_min_batch &&
+                         fused_supported(B * S, S, c->P, B, sms_n);
   auto fill_loop = [&](LoopParams& lp) {
     for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
       const pi0_gemma_layer_w& lw = w.exp[l];
@@ -822,6 +857,27 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
       lp.n_steps = 1;
       lp.layers_only = 1;
       PI0_TRY(loop_denoise(lp, c->mega_ctas, s));
+    } else if (use_fused) {
+      // rollout batches: all expert layers of this step in one persistent tcgen05 launch (fused_denoise.cu)
+      PROF("denoise.layers_fused");
+      FusedParams fp = {};
+      fp.gd = c->fused_descs;
+      for (int l = 0; l < c->cfg.n_gemma_layers; ++l) { fp.g1[l] = w.exp[l].g1; fp.g2[l] = w.exp[l].g2; }
+      fp.n_layers = c->cfg.n_gemma_layers;
+      fp.M = B * S; fp.S = S; fp.P = c->P; fp.B = B;
+      fp.x0 = (const bf16*)c->suf; fp.x = (bf16*)c->xe; fp.y = (bf16*)c->ye; fp.h = (bf16*)c->he; fp.q = (bf16*)c->qe;
+      fp.att = (bf16*)c->att_e; fp.act = (bf16*)c->act_e;
+      fp.partial = c->fused_partial;
+      fp.partial_elems = (long long)(fused_partial_bytes(c->maxB * S, sms_n) / sizeof(float));
+      fp.kcache = (bf16*)c->kcache; fp.vtcache = (bf16*)c->vtcache;
+      fp.kc_layer_stride = (long long)c->maxB * c->kv_pitch * kHd;
+      fp.vt_layer_stride = (long long)c->maxB * kHd * c->vt_pitch;
+      fp.kv_pitch = c->kv_pitch; fp.vt_pitch = c->vt_pitch;
+      fp.rope_cos = w.rope_cos; fp.rope_sin = w.rope_sin; fp.pos_ids = c->suffix_pos; fp.pad = c->pad; fp.cum = c->suffix_cum;
+      fp.sync = c->fused_sync;
+      fp.kp = (c->P + S + 31) / 32 * 32;
+      fp.hpg = B * 2 <= sms_n ? 4 : 8;
+      PI0_TRY(fused_denoise_layers(fp, sms_n, s));
     } else if (c->mega_ctas > 0 && B * S <= c->mega_max_rows && mega_supported(B * S, S, c->P)) {
       // latency regime: all expert layers of this step in one persistent cooperative launch
       PROF("denoise.layers_mega");

@@ -110,3 +110,44 @@ def test_persistent_kernel_with_chunked_operand_staging_for_batch_4_to_9(cuda, B
     print(f"\n[persistent kernel B={B}] vs oracle {err:.3e}; vs per-op launches {dif:.3e}")
     assert err <= 1e-2, err
     assert dif <= 1e-2, dif
+
+
+def _fused_engine(packed, B, on, **kw):
+    old = os.environ.get("PI0_FUSED")
+    os.environ["PI0_FUSED"] = "1" if on else "0"
+    try:
+        return Pi0Engine(packed, max_batch=B, use_cuda_graph=kw.pop("graph", False), **kw)
+    finally:
+        if old is None:
+            os.environ.pop("PI0_FUSED", None)
+        else:
+            os.environ["PI0_FUSED"] = old
+
+
+@pytest.mark.parametrize("B,n_valid", [(7, [72, 9, 33, 2, 50, 17, 64]), (16, [72, 9, 33, 2, 50, 17, 64, 1]),
+                                       (64, [72, 9, 33, 2, 50, 17, 64, 1, 12, 40, 72])])
+def test_fused_tcgen05_denoise_step_kernel_matches_per_op_path_and_oracle(cuda, B, n_valid):
+    """Rollout batches: the 18 expert layers of an Euler step as ONE persistent tcgen05 launch (split-K partial GEMMs, reduce
+    phases carrying RoPE / residual + norm / GeGLU, in-kernel batch attention) against the per-op launches and the oracle."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=3, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=5)
+    packed = PackedWeights(sd, cuda, torch.bfloat16)
+    inp = synthetic_inputs(B, vocab=dims.vocab, n_valid_text=n_valid)
+    args = _args(cuda, inp)
+    e_f = _fused_engine(packed, B, True)
+    assert e_f.path_report(B)["denoise"] == "fused_tcgen05_layers_kernel_per_step"
+    fused = e_f.sample_actions(*args)
+    e_p = _fused_engine(packed, B, False)
+    assert e_p.path_report(B)["denoise"] == "tcgen05_per_op"
+    per_op = e_p.sample_actions(*args)
+    torch.cuda.synchronize()
+    assert torch.isfinite(fused).all()
+    rows = list(range(B)) if B <= 16 else [0, 1, 31, 63]
+    sub = ([i[rows] for i in inp[0]], [m[rows] for m in inp[1]], inp[2][rows], inp[3][rows], inp[4][rows], inp[5][rows])
+    ref = oracle_for(sd, dims, 1, 72, 4, "bf16").sample_actions(*sub)
+    err = (fused.cpu()[rows] - ref).abs().max().item()
+    dif = (fused - per_op).abs().max().item()
+    print(f"\n[fused denoise step B={B}] vs oracle {err:.3e}; vs per-op launches {dif:.3e}; launches "
+          f"{e_f.lib.pi0_launch_count(0)}")
+    assert err <= 1e-2, err
+    assert dif <= 1e-2, dif
