@@ -16,6 +16,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/pi0b200.h"
 #include "denoise_loop.cuh"
 #include "fused_denoise.cuh"
@@ -88,6 +90,7 @@ struct pi0_ctx {
   bool guarded;  // PI0_GUARD: 1 KiB 0xA5 zones behind every buffer
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
   bool prof_on;
+  bool nvtx_on;  // PI0_NVTX=1
   struct ProfRec { const char* label; cudaEvent_t e0, e1; };
   std::vector<ProfRec> prof;
 };
@@ -95,16 +98,22 @@ struct pi0_ctx {
 namespace {
 
 // Records a CUDA-event pair around the launches issued while it is alive (only when profiling is enabled).
+// With PI0_NVTX=1 every phase is also an NVTX range (same labels), so that `ncu --nvtx --nvtx-include "prefill.attention/"`
+// or a timeline tool can select a phase by name (tracing).
 struct ProfScope {
-  pi0_ctx* c; cudaStream_t s; cudaEvent_t e1;
-  ProfScope(pi0_ctx* ctx, const char* label, cudaStream_t st) : c(ctx), s(st), e1(nullptr) {
+  pi0_ctx* c; cudaStream_t s; cudaEvent_t e1; bool nvtx;
+  ProfScope(pi0_ctx* ctx, const char* label, cudaStream_t st) : c(ctx), s(st), e1(nullptr), nvtx(ctx->nvtx_on) {
+    if (nvtx) nvtxRangePushA(label);
     if (!c->prof_on) return;
     cudaEvent_t e0;
     if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { e1 = nullptr; return; }
     cudaEventRecord(e0, s);
     c->prof.push_back(pi0_ctx::ProfRec{label, e0, e1});
   }
-  ~ProfScope() { if (e1) cudaEventRecord(e1, s); }
+  ~ProfScope() {
+    if (e1) cudaEventRecord(e1, s);
+    if (nvtx) nvtxRangePop();
+  }
 };
 #define PROF(label) ProfScope _prof_scope(c, label, s)
 
@@ -422,6 +431,7 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
   c->w = *w;
   c->nbufs = 0;
   c->prof_on = false;
+  c->nvtx_on = getenv("PI0_NVTX") && strcmp(getenv("PI0_NVTX"), "0") != 0;
   uintptr_t b = ((uintptr_t)workspace + 1023) & ~(uintptr_t)1023;
   c->base = (uint8_t*)b;
   c->ws_bytes = workspace_bytes;

@@ -198,3 +198,21 @@ def test_no_kernel_writes_outside_its_workspace_buffer(cuda, monkeypatch, B, n_c
         eng.workspace[off + n.value * 2] = 7
         with pytest.raises(Exception, match="suffix.q"):
             eng.check_guards()
+
+
+def test_unshrunk_action_out_proj_error_is_reported_next_to_the_tolerance(cuda):
+    """`random_state_dict` shrinks action_out_proj by 0.25 so that |v_t| < 1 like a trained policy on bound-normalised actions
+    (one bf16 ulp of v_t at |v_t| ~ 3 is 1.6e-2 > the 1e-2 tolerance for ANY two bf16 implementations). This case undoes the
+    shrink, reports the error, and bounds it RELATIVE to the velocity scale: the kernels are as accurate as before, only the
+    quantity is 4x larger."""
+    dims = Dims(vocab=4096)
+    sd = random_state_dict(dims, device=cuda, seed=0)
+    sd["model.action_out_proj.weight"] = (sd["model.action_out_proj.weight"].float() * 4.0).to(torch.bfloat16)
+    inp = synthetic_inputs(1, vocab=dims.vocab, n_valid_text=[12])
+    _, out = _engine_out(cuda, sd, "bf16", 1, inp)
+    ref = oracle_for(sd, dims, 1, 72, 4, "bf16").sample_actions(*inp)
+    err = (out - ref).abs().max().item()
+    moved = (ref - inp[5]).abs().max().item()
+    print(f"\n[full depth bf16, un-shrunk action_out_proj] max-abs action error {err:.3e} for |actions - noise|max {moved:.3f} "
+          f"(relative {err / moved:.2e}; shrunk weights: 4.6e-3 for 0.64)")
+    assert err / moved <= 1.5e-2
