@@ -54,19 +54,55 @@ struct TcShape {
   int kb_per_split;  // k-blocks (of kBK) per split
   uint32_t stage_tx; // bytes one pipeline stage receives: A box (rows clipped to M for a single short M tile) + W box
   int tma_store;     // 1: EPI_STORE / EPI_GEGLU output goes through shared memory and tensor-map stores (tmC valid)
+  int super_m, super_n;  // second-level tile blocking for wide problems (tiles), see tile_coords
 };
 
+// Tile order of the persistent kernels. Small problems: groups of kGroupM M-tiles, M fastest inside a group, so that the
+// CTAs in flight share a W tile column-wise and a handful of A tiles. Wide problems (prefill gate/up: 82 x 128 tiles of
+// 256 x 256 at batch 64) add a second level: super-blocks of kSuperM x kSuperN tiles whose A block (32 x 256 rows x K) and W
+// block (32 x 256 rows x K) are 33.5 MB each at K = 2048 and stay resident in the 126 MB L2 while the block's 1024 tiles
+// run; the A block is reused by the next super-block of the same rows. With the one-level order the whole W panel (134 MB,
+// larger than L2) was re-streamed from HBM for every group of 8 M-tiles: 3.0 GB of DRAM reads per launch against 0.22 GB of
+// operands (ncu, profiles/r02_gateup_pair_b64_full_raw.csv).
+// Defaults from a sweep on the batch-64 gate/up GEMM (tools/sweep_super_tiles.sh, DRAM read per launch / kernel time):
+// one level 1.9-3.0 GB / 1.81 ms; 32 x 32 1.07 GB / 1.766 ms; 41 x 32 0.96 GB / 1.764 ms; 82 x 16 0.93 GB / 1.756 ms.
+// => N panels of 16 tiles (W block 16.8 MB at K = 2048, resident) and an A block of ~84 MB worth of rows streamed per
+// panel and largely kept by the L2 from one panel to the next. PI0_SUPER_M / PI0_SUPER_N override (development knobs).
+constexpr int kSuperN = 16;
+constexpr long long kSuperABytes = 84ll << 20;
+static void set_super(TcShape& sh, int tile_rows) {
+  static int sm = getenv("PI0_SUPER_M") ? atoi(getenv("PI0_SUPER_M")) : 0;
+  static int sn = getenv("PI0_SUPER_N") ? atoi(getenv("PI0_SUPER_N")) : 0;
+  long long auto_m = kSuperABytes / ((long long)tile_rows * sh.K * 2);
+  if (auto_m < kGroupM) auto_m = kGroupM;
+  if (auto_m > (1 << 20)) auto_m = 1 << 20;
+  sh.super_m = sm > 0 ? sm : (int)auto_m;
+  sh.super_n = sn > 0 ? sn : kSuperN;
+}
 __device__ __forceinline__ void tile_coords(const TcShape& sh, int idx, int& z, int& tm, int& tn) {
   int per_z = sh.tiles_m * sh.tiles_n;
   z = idx / per_z;
   int r = idx - z * per_z;
-  int span = kGroupM * sh.tiles_n;
+  int first_sm = 0, sm_sz = sh.tiles_m, first_n = 0, sn_sz = sh.tiles_n;
+  if (sh.tiles_n > sh.super_n && sh.tiles_m > kGroupM) {
+    const int sm_span = sh.super_m * sh.tiles_n;
+    const int sg = r / sm_span;
+    first_sm = sg * sh.super_m;
+    sm_sz = min(sh.tiles_m - first_sm, sh.super_m);
+    r -= sg * sm_span;
+    const int sn_span = sm_sz * sh.super_n;
+    const int ng = r / sn_span;
+    first_n = ng * sh.super_n;
+    sn_sz = min(sh.tiles_n - first_n, sh.super_n);
+    r -= ng * sn_span;
+  }
+  int span = kGroupM * sn_sz;
   int g = r / span;
   int first_m = g * kGroupM;
-  int gsz = min(sh.tiles_m - first_m, kGroupM);
+  int gsz = min(sm_sz - first_m, kGroupM);
   int rr = r - g * span;
-  tm = first_m + rr % gsz;
-  tn = rr / gsz;
+  tm = first_sm + first_m + rr % gsz;
+  tn = first_n + rr / gsz;
 }
 
 // Epilogue of one 128-row accumulator tile: TMEM lanes of this warp's quadrant -> registers -> fused epilogue -> global.
@@ -790,6 +826,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   sh.tiles_m = (g.M + kBM - 1) / kBM;
   sh.tiles_n = (g.N + BN - 1) / BN;
   sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
+  set_super(sh, kBM);
   const int num_k = (g.K + kBK - 1) / kBK;
   sh.splits = 1;
   sh.kb_per_split = num_k;
@@ -863,6 +900,7 @@ static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   sh.tiles_m = (g.M + 2 * kBM - 1) / (2 * kBM);   // 256-row tiles, one per CTA pair
   sh.tiles_n = (g.N + BN - 1) / BN;
   sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
+  set_super(sh, 2 * kBM);
   sh.splits = 1;
   sh.kb_per_split = (g.K + kBK - 1) / kBK;
   sh.stage_tx = 2 * Cfg::kStageBytes;
