@@ -206,9 +206,14 @@ class LeRobotPolicyWrapper:
             if hasattr(self.model, "reset"):
                 self.model.reset()
             actions = self.model.infer_action(batch)[:, : self.action_step]
+        # one post-processing launch + one D2H for the whole group (element-wise per action row, so slicing the result gives
+        # exactly what per-request calls would); a single-observation request gets its [action_step, 7] array without batch dim
+        post = self.env_adapter.postprocess(actions.float() if actions.shape[0] > 1 else actions[0].float())
+        if actions.shape[0] == 1:
+            post = post[None]
         o = 0
         for (i, _), n in zip(pre, sizes):
-            a = actions[o:o + n]
+            a = post[o:o + n]
             o += n
-            out[i] = self.env_adapter.postprocess((a[0] if n == 1 else a).float())
+            out[i] = np.ascontiguousarray(a[0] if n == 1 else a)
         return out
