@@ -73,7 +73,9 @@ int pi0_prefill_attention(const void* q, const void* kcache, const void* vtcache
 }
 
 int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream) {
-  return siglip_attention(qkv, att, B, (cudaStream_t)stream);
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return siglip_attention(qkv, att, B, sms, (cudaStream_t)stream);
 }
 
 int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,

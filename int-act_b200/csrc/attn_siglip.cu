@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(256, 1) siglip_attn_kernel(const bf16* __restr
 
 }  // namespace
 
-int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s) {
+int siglip_attention_mma(const void* qkv, void* att, int B, cudaStream_t s) {
   PI0_REQUIRE(qkv && att && B >= 1, "siglip_attention: bad argument");
   static PerDeviceOnce attr_once;
   if (attr_once.need()) {
@@ -171,6 +171,16 @@ int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s) {
                             (const bf16*)qkv, (bf16*)att, 0.11785113019775793f));
   ++g_launch_count;
   return 0;
+}
+
+// The tcgen05 kernel (attn_siglip_tc.cu) is the product path; PI0_SIGLIP_ATTN=mma keeps this one selectable for comparison.
+bool siglip_attention_use_tc() {
+  const char* e = getenv("PI0_SIGLIP_ATTN");
+  return !(e && e[0] == 'm');
+}
+int siglip_attention(const void* qkv, void* att, int B, int num_sms, cudaStream_t s) {
+  if (siglip_attention_use_tc()) return siglip_attention_tc(qkv, att, B, num_sms, s);
+  return siglip_attention_mma(qkv, att, B, s);
 }
 
 }  // namespace pi0

@@ -36,7 +36,10 @@ int decode_attention_batch(const void* q, const void* kcache, const void* vtcach
                            const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, cudaStream_t s);
 
 // fused SigLIP self-attention (attn_siglip.cu), bf16 only: fused q|k|v [B*256, 3456] -> att [B*256, 1152]
-int siglip_attention(const void* qkv, void* att, int B, cudaStream_t s);
+int siglip_attention(const void* qkv, void* att, int B, int num_sms, cudaStream_t s);   // dispatcher (attn_siglip.cu)
+int siglip_attention_mma(const void* qkv, void* att, int B, cudaStream_t s);
+int siglip_attention_tc(const void* qkv, void* att, int B, int num_sms, cudaStream_t s);
+bool siglip_attention_use_tc();
 // fused prefix-prefill attention on tcgen05 (attn_prefill.cu); q / att [B*T][8*256], P <= 336 prefix keys
 bool prefill_attention_supported(int T, int P);
 int prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B, int T,

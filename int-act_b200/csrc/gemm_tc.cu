@@ -779,7 +779,8 @@ static int make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0
 int tc_make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0, int64_t sz1,
                 int box_rows, int box_k, int swizzle_bytes) {
   return make_map(map, base, K, rows, nz0, nz1, ld, sz0, sz1, box_rows, box_k,
-                  swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+                  swizzle_bytes == 0 ? CU_TENSOR_MAP_SWIZZLE_NONE
+                                     : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 // Output tensor map of the TMA-store epilogue ({columns, rows, z0, z1}, 32 x 32 box, 64-byte swizzle) when the epilogue

@@ -587,7 +587,8 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
   const int S = c->S, P = c->P, M = B * S;
   const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
   const char* gemm = c->cfg.dtype == 1 || c->cfg.gemm_impl == 1 ? "simt_fp32_check" : "tcgen05";
-  const char* siglip_attn = bf && c->siglip_fused ? "fused_mma_sync" : "gemm_softmax_gemm";
+  const char* siglip_attn = bf && c->siglip_fused ? (siglip_attention_use_tc() ? "fused_tcgen05" : "fused_mma_sync")
+                                                  : "gemm_softmax_gemm";
   const bool pf = bf && c->prefill_fused && prefill_attention_supported(P, P) &&
                   (int64_t)B * ((P * kHeads + 127) / 128) >= c->prefill_fused_min_tiles;
   const char* prefill_attn = pf ? "fused_tcgen05" : "gemm_softmax_gemm";
@@ -685,7 +686,7 @@ int pi0_siglip_forward(pi0_ctx* c, int B, int cam, const float* images, float sc
     if (fused_attn) {
       // scores + softmax + P.V of all heads in one launch (attn_siglip.cu)
       PROF("siglip.attention");
-      PI0_TRY(siglip_attention(c->qk_s, c->att_s, B, s));
+      PI0_TRY(siglip_attention(c->qk_s, c->att_s, B, c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
     } else {
     {  // scores[b,h] = rnd(rnd(q k^T) * 72^-0.5), bidirectional
       GemmProblem g = gemm_problem(c->qk_s, qk_ld, at(c->qk_s, kVisHidden, es), qk_ld, kPatches, kPatches, kVisHd);

@@ -177,18 +177,23 @@ def test_decode_attention_fused(cuda, B, S, P):
         assert err3 <= 2 ** -6 * max(1.0, ref.abs().max().item()), err3
 
 
-@pytest.mark.parametrize("B", [1, 3])
-def test_siglip_attention_fused(cuda, B):
-    """Fused SigLIP attention (attn_siglip.cu) against a torch restatement with the reference's rounding points:
-    bf16 scores scaled by 72^-0.5, fp32 softmax, bf16 probabilities, bf16 output."""
+@pytest.mark.parametrize("mode", ["tc", "mma"])
+@pytest.mark.parametrize("B", [1, 3, 12])
+def test_siglip_attention_fused(cuda, B, mode, monkeypatch):
+    """Fused SigLIP attention against a torch restatement with the reference's rounding points: bf16 scores scaled by
+    72^-0.5, fp32 softmax, bf16 probabilities, bf16 output. mode "tc" = the tcgen05 kernel (attn_siglip_tc.cu, the product
+    path; B = 12 gives every CTA of the persistent grid more than one (image, head) item), "mma" = the mma.sync kernel it
+    replaced (attn_siglip.cu, PI0_SIGLIP_ATTN=mma)."""
+    monkeypatch.setenv("PI0_SIGLIP_ATTN", mode)
     g = torch.Generator().manual_seed(9)
     T, H, D = 256, 16, 72
     qk = (torch.randn((B * T, 2 * H * D), generator=g) * 1.5).bfloat16()
     v = torch.randn((B, H, T, D), generator=g).bfloat16()
     qkv = torch.cat([qk, v.transpose(1, 2).reshape(B * T, H * D)], dim=1).contiguous()     # [B*256, 3456]
-    att = torch.zeros((B * T, H * D), dtype=torch.bfloat16, device=cuda)
+    att = torch.full((B * T, H * D), float("nan"), dtype=torch.bfloat16, device=cuda)
     dqkv = qkv.to(cuda)
-    pb.check(pb.lib().pi0_siglip_attention(pb.ptr(dqkv), pb.ptr(att), B, _stream()), "pi0_siglip_attention")
+    for _ in range(2):   # the second launch re-uses the TMEM / barrier state conventions from a fresh kernel: must agree
+        pb.check(pb.lib().pi0_siglip_attention(pb.ptr(dqkv), pb.ptr(att), B, _stream()), "pi0_siglip_attention")
     torch.cuda.synchronize()
     q = qk[:, : H * D].float().view(B, T, H, D).transpose(1, 2)
     k = qk[:, H * D:].float().view(B, T, H, D).transpose(1, 2)
@@ -196,6 +201,7 @@ def test_siglip_attention_fused(cuda, B):
     sc = (sc * torch.tensor(72 ** -0.5, dtype=torch.float32)).bfloat16().float()
     pr = torch.softmax(sc, dim=-1).bfloat16().float()
     ref = (pr @ v.float()).bfloat16().float().transpose(1, 2).reshape(B * T, H * D)
+    assert torch.isfinite(att.float()).all()
     err = (att.float().cpu() - ref).abs().max().item()
     assert err <= 2 ** -6 * max(1.0, ref.abs().max().item()), err
 

@@ -168,7 +168,7 @@ def test_path_report_names_the_variant_every_phase_takes(cuda):
     b1, b64 = eng.path_report(1), eng.path_report(64)
     assert b1["denoise"] == "persistent_layers_kernel_per_step" and b1["prefill_attention"] == "gemm_softmax_gemm"
     assert b64["denoise"] == "tcgen05_per_op" and b64["denoise_attention"] == "batch_cta_pair_per_sample"
-    assert b64["prefill_attention"] == "fused_tcgen05" and b64["siglip_attention"] == "fused_mma_sync"
+    assert b64["prefill_attention"] == "fused_tcgen05" and b64["siglip_attention"] == "fused_tcgen05"
     lib = Pi0Engine(packed, n_cams=2, horizon=16, max_batch=64).path_report(64)      # LIBERO shape: P = 584 > 336
     assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "gemm_softmax_gemm"
     f32 = Pi0Engine(PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.float32), dtype="fp32")
