@@ -15,7 +15,8 @@
 //              K-major P tile (A operand of the second product)
 //   O = P V    V is consumed as it lies in the activation (row-major [key][dim] = MN-major B operand): N = 64 dims from the
 //              swizzled tile + N = 16 from {tail, zero}, 16 k-steps of 16 keys; O of half h overwrites S_h in TMEM
-//   epilogue   O -> rnd -> bf16, nine 16-byte stores per row into att [tokens, 1152]
+//   epilogue   O -> rnd -> bf16 -> [128 rows x 144 B] staging tile (conflict-free 16-byte stores) -> one TMA store per half
+//              into att [tokens, 1152]
 // The S product of half 1 runs under the softmax of half 0, P.V of half 0 under the softmax of half 1, the next item's Q | K
 // load as soon as both S products have been issued.
 #include "elementwise.cuh"
