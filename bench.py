@@ -254,6 +254,80 @@ def time_gpu_eager(workload, B, dev, steps=3, b1_iters=20, log=None):
     return out
 
 
+def time_fp32_regime(workload, dev, B=8, steps=2, b1_iters=10, log=None):
+    """`--use_bf16 False`, the flag the reference's shipped eval scripts pass (slurms/eval_scripts/simpler/
+    ev_pi0_bridge_simpler.sh:99, doc/evaluation.md:152): fp32 weights and autocast(float32), i.e. plain fp32. Here that
+    regime is the SIMT fp32 path (csrc/gemm_simt.cu, parity <= 1e-4); this leg times it next to PyTorch eager fp32 (cuBLAS
+    SGEMM, TF32 off as torch defaults) on the same GPU, same weights / inputs / noise."""
+    from int_act_b200.policy import PI0Policy
+    from int_act_b200.weights import Dims, random_state_dict
+    from oracle.pi0_eager import Pi0Eager
+    from oracle.pi0_oracle import OracleDims
+
+    n_cams, lang_len, horizon = WORKLOADS[workload]
+    dims = Dims()
+    sd = random_state_dict(dims, device=dev, seed=0)
+    policy = PI0Policy(make_config(workload), state_dict=sd, max_batch=B, device=dev)
+    policy.to(torch.float32)
+    eng = policy._ensure_engine(B)
+    policy._state_dict = None
+
+    def timed(fn, n):
+        ts = []
+        for _ in range(n):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ts.sort()
+        return ts
+
+    out = {"batch": B, "dtype": "f32"}
+    eng._static(B)["x_t"].normal_()
+    eng._run_static(B)
+    ts = timed(lambda: eng._run_static(B), steps)
+    ours_b = sum(ts) / len(ts)
+    eng._static(1)["x_t"].normal_()
+    eng._run_static(1)
+    ts = timed(lambda: eng._run_static(1), b1_iters)
+    ours_1 = ts[len(ts) // 2]
+    out["b200"] = {"value": B / (ours_b * 1e-3), "unit": "chunks/s", "ms_per_step": ours_b, "p50_b1_ms": ours_1,
+                   "path": eng.path_report(B)}
+    if log:
+        log(f"fp32 regime, this library: batch {B} {ours_b:.1f} ms/step, batch 1 {ours_1:.1f} ms")
+    del policy, eng
+    torch.cuda.empty_cache()
+
+    model = Pi0Eager(OracleDims(n_cams=n_cams, lang_len=lang_len, horizon=horizon), sd, dev, use_bf16=False)
+    del sd
+    torch.cuda.empty_cache()
+
+    def inputs(b):
+        obs = synthetic_observations(b, n_cams, lang_len, seed=1234, pinned=False)
+        imgs = [obs[k].to(dev) for k in obs if k.startswith("observation.images")]
+        masks = [torch.ones(b, dtype=torch.bool, device=dev) for _ in imgs]
+        noise = torch.normal(0.0, 1.0, (b, horizon, 32), generator=torch.Generator().manual_seed(42)).to(dev)
+        return imgs, masks, obs["lang_tokens"].to(dev), obs["lang_masks"].to(dev), obs["observation.state"].to(dev), noise
+
+    ab, a1 = inputs(B), inputs(1)
+    model.sample_actions(*ab)
+    ts = timed(lambda: model.sample_actions(*ab), steps)
+    eager_b = sum(ts) / len(ts)
+    model.sample_actions(*a1)
+    ts = timed(lambda: model.sample_actions(*a1), b1_iters)
+    eager_1 = ts[len(ts) // 2]
+    out["eager"] = {"value": B / (eager_b * 1e-3), "unit": "chunks/s", "ms_per_step": eager_b, "p50_b1_ms": eager_1,
+                    "what": f"PyTorch eager fp32 (cuBLAS SGEMM, allow_tf32={torch.backends.cuda.matmul.allow_tf32}), torch "
+                            f"{torch.__version__}"}
+    out["speedup_batch"] = out["b200"]["value"] / out["eager"]["value"]
+    out["speedup_b1_latency"] = eager_1 / ours_1
+    del model
+    torch.cuda.empty_cache()
+    return out
+
+
 def eager_arm(args, rank, local_rank):
     """`--impl eager`: the GPU-eager baseline as its own JSON line (rank 0 only; replicas would time the same thing)."""
     if rank != 0:
@@ -614,6 +688,8 @@ def b200_arm(args, rank, world, local_rank):
             ge["speedup_batch"] = value / world / ge["value"]
             ge["speedup_b1_latency"] = ge["p50_b1_ms"] / p50
             line["gpu_eager"] = ge
+        if args.fp32_regime and world == 1:
+            line["fp32_regime"] = time_fp32_regime(args.workload, dev)
 
         # ---- (5) CPU baseline on the host cores (N=1 only) --------------------------------------------------------
         if world == 1 and not args.no_cpu_baseline:
@@ -639,6 +715,8 @@ def main():
     ap.add_argument("--latency-iters", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-eager", action="store_true")
+    ap.add_argument("--fp32-regime", action="store_true",
+                    help="also time the --use_bf16 False regime (SIMT fp32 path) next to PyTorch eager fp32")
     ap.add_argument("--no-configs", action="store_true", help="skip the C3-strong / C4 / C5 side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
