@@ -201,6 +201,16 @@ int pi0_decode_attention(const void* q, const void* kcache, const void* vtcache,
 int pi0_decode_attention_split(const void* q, const void* kcache, const void* vtcache, void* att, void* scratch,
                                const uint8_t* pad, const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch,
                                void* stream);
+/* pi0_decode_attention_split without a scratch argument and without any allocation: the score scratch lives in a 4 MiB
+ * static __device__ array inside the library (pi0_decode_attention_split_static_max_bytes()), for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). No counterpart in the reference.
+ * Needs B*8*S*roundup(P+S, 32)*2 bytes <= the maximum, else -2 with a message
+ * (bridge shapes: up to batch 145). Every call on a GPU shares the one array and nothing is cleared (the scores kernel
+ * writes every element the second kernel reads): calls that overlap on the same GPU - two streams, two threads - RACE;
+ * serialise them or use pi0_decode_attention_split with caller-owned scratch. Output bit-identical to that entry. */
+int pi0_decode_attention_split_static(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                                      const int32_t* cum, int B, int S, int P, int kv_pitch, int vt_pitch, void* stream);
+long long pi0_decode_attention_split_static_max_bytes(void);
 /* The same attention with one CTA per sample and the sample's K / V^T tiles staged in shared memory (attn_batch.cu):
  * the rollout-batch path (B >= 4). S <= 6, P+S <= 352. */
 int pi0_decode_attention_batch(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,

@@ -107,6 +107,9 @@ SIGNATURES = {
                                         C.c_int, c_ptr]),
     "pi0_decode_attention_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                              C.c_int, c_ptr]),
+    "pi0_decode_attention_split_static": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
+                                                    C.c_int, C.c_int, c_ptr]),
+    "pi0_decode_attention_split_static_max_bytes": (C.c_longlong, []),
     "pi0_decode_attention_split": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
                                              C.c_int, C.c_int, c_ptr]),
     "pi0_position_ids": (C.c_int, [c_ptr, C.c_int, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr]),

@@ -10,6 +10,13 @@
 // [mirror] src/model/mvla/mllm.py:265-317; suffix mask modeling_mvla.py:686-692,817-821).
 #include "attn_split.cuh"
 
+// Scratch of the allocation-free entry point (pi0_decode_attention_split_static, bottom of this file): the bf16 score
+// matrix [B*8*S, roundup(P+S, 32)] that pi0_decode_attention_split takes from the caller. File scope, 4 MiB: every GPU that
+// loads the library holds it until the process exits. In HOST code this name is only a stand-in for the symbol - never a
+// device address; the host side resolves it with cudaGetSymbolAddress (once per device, below) and hands that pointer on.
+constexpr size_t kSplitStaticScratchBytes = (size_t)4 << 20;
+static __device__ __align__(256) unsigned char g_split_static_scratch[kSplitStaticScratchBytes];
+
 namespace pi0 {
 
 namespace {
@@ -126,4 +133,44 @@ int decode_attention_split(const void* q, const void* kcache, const void* vtcach
   return 0;
 }
 
+// Device address of g_split_static_scratch on the CURRENT device, resolved once per device (a symbol has one instance per
+// GPU that loaded the module, each with its own address).
+static int split_static_scratch(void** out) {
+  static void* ptr[64] = {};
+  int dev = -1;
+  PI0_CHECK_CUDA(cudaGetDevice(&dev));
+  PI0_REQUIRE(dev >= 0 && dev < 64, "decode_attention_split_static: device ordinal %d outside [0, 64)", dev);
+  if (ptr[dev] == nullptr) {
+    void* p = nullptr;
+    PI0_CHECK_CUDA(cudaGetSymbolAddress(&p, g_split_static_scratch));
+    PI0_REQUIRE(p != nullptr, "decode_attention_split_static: null symbol address");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+int decode_attention_split_static(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad,
+                                  const int* cum, int B, int S, int P, int kv_pitch, int vt_pitch, cudaStream_t s) {
+  PI0_REQUIRE(q && kcache && vtcache && att && pad && cum && B >= 1, "decode_attention_split_static: bad argument");
+  PI0_REQUIRE(decode_attention_split_supported(S, P), "decode_attention_split_static: S=%d P=%d unsupported", S, P);
+  const size_t need = (size_t)B * 8 * S * ((size_t)(P + S + 31) / 32 * 32) * sizeof(bf16);
+  PI0_REQUIRE(need <= kSplitStaticScratchBytes,
+              "decode_attention_split_static: B=%d S=%d P=%d needs %zu bytes of score scratch, the built-in buffer holds %zu "
+              "(use pi0_decode_attention_split with caller-owned scratch)", B, S, P, need, kSplitStaticScratchBytes);
+  void* scratch = nullptr;
+  PI0_TRY(split_static_scratch(&scratch));
+  // nothing to clear: decode_scores_kernel writes every score element that decode_pv_kernel reads
+  return decode_attention_split(q, kcache, vtcache, att, scratch, pad, cum, B, S, P, kv_pitch, vt_pitch, s);
+}
+
 }  // namespace pi0
+
+extern "C" int pi0_decode_attention_split_static(const void* q, const void* kcache, const void* vtcache, void* att,
+                                                 const uint8_t* pad, const int32_t* cum, int B, int S, int P, int kv_pitch,
+                                                 int vt_pitch, void* stream) {
+  return pi0::decode_attention_split_static(q, kcache, vtcache, att, pad, cum, B, S, P, kv_pitch, vt_pitch,
+                                            (cudaStream_t)stream);
+}
+
+extern "C" long long pi0_decode_attention_split_static_max_bytes(void) { return (long long)kSplitStaticScratchBytes; }
