@@ -185,6 +185,14 @@ typedef struct pi0_gemm_desc {
 /* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT, 2 = tcgen05 single-CTA kernels
    only, 3 = force the tcgen05 CTA-pair (cta_group::2) kernel. */
 int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream);
+/* The GEMM of the fp32 regime on the tensor cores (csrc/gemm_x3.cu): fp32 A, W, bias / residual / out; every operand is
+ * split into three bf16 pieces (hi + mid + lo = the fp32 value exactly), the six piece products >= 2^-16 are one bf16 tcgen05
+ * GEMM over K' = 6 K with fp32 accumulation and fp32 epilogues. Replaces torch.matmul / nn.Linear in fp32 (the reference with
+ * `--use_bf16 False`, slurms/eval_scripts/simpler/ev_pi0_bridge_simpler.sh:99). scratch_a / scratch_w: device buffers of
+ * pi0_gemm_f32x3_scratch_bytes(nz0 * nz1, M | N, K) bytes. */
+int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
+                   void* stream);
+size_t pi0_gemm_f32x3_scratch_bytes(int64_t nz, int64_t rows, int K);
 
 int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream);
 int pi0_layernorm(const void* x, void* y, const float* w, const float* b, int M, int D, int dtype, void* stream);

@@ -107,6 +107,8 @@ SIGNATURES = {
                                         C.c_int, c_ptr]),
     "pi0_decode_attention_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                              C.c_int, c_ptr]),
+    "pi0_gemm_f32x3": (C.c_int, [C.POINTER(GemmDesc), c_ptr, C.c_size_t, c_ptr, C.c_size_t, C.c_int, c_ptr]),
+    "pi0_gemm_f32x3_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
     "pi0_decode_attention_split_static": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, C.c_int, c_ptr]),
     "pi0_decode_attention_split_static_max_bytes": (C.c_longlong, []),
@@ -193,5 +195,15 @@ def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bia
     d.vt_hd = d.vt_heads = d.vt_rpb = 1
     for k, v in extra.items():
         setattr(d, k, ptr(v) if hasattr(v, "data_ptr") else v)
+    if impl == "x3":  # the fp32 regime's split-bf16 tensor-core GEMM, scratch owned by this helper
+        import torch
+        nz = d.nz0 * d.nz1
+        ba = int(lib().pi0_gemm_f32x3_scratch_bytes(nz, d.M, d.K))
+        bw = int(lib().pi0_gemm_f32x3_scratch_bytes(nz, d.N, d.K))
+        sa = torch.empty(ba, dtype=torch.uint8, device=out.device)
+        sw = torch.empty(bw, dtype=torch.uint8, device=out.device)
+        check(lib().pi0_gemm_f32x3(C.byref(d), ptr(sa), ba, ptr(sw), bw, num_sms, current_stream()), "pi0_gemm_f32x3")
+        torch.cuda.synchronize()   # the scratch tensors die with this frame
+        return out
     check(lib().pi0_gemm(C.byref(d), dtype, impl, num_sms, current_stream()), "pi0_gemm")
     return out

@@ -16,9 +16,9 @@ long long pi0_launch_count(int reset) {
   return v;
 }
 
-int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream) {
+static int problem_from_desc(const pi0_gemm_desc* d, GemmProblem& g) {
   PI0_REQUIRE(d != nullptr, "pi0_gemm: null descriptor");
-  GemmProblem g = gemm_problem(d->A, d->lda, d->W, d->ldw, d->M, d->N, d->K);
+  g = gemm_problem(d->A, d->lda, d->W, d->ldw, d->M, d->N, d->K);
   g.a_z0 = d->a_z0; g.a_z1 = d->a_z1; g.w_z0 = d->w_z0; g.w_z1 = d->w_z1;
   g.nz0 = d->nz0 > 0 ? d->nz0 : 1;
   g.nz1 = d->nz1 > 0 ? d->nz1 : 1;
@@ -39,8 +39,27 @@ int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* str
   e.rope_cos = d->rope_cos; e.rope_sin = d->rope_sin; e.pos_ids = d->pos_ids;
   e.kcache = d->kcache; e.n_q_heads = d->n_q_heads; e.kv_pitch = d->kv_pitch;
   e.dt = d->dt;
+  return 0;
+}
+
+int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* stream) {
+  GemmProblem g;
+  PI0_TRY(problem_from_desc(d, g));
   return gemm_launch(g, dtype, impl, num_sms, (cudaStream_t)stream);
 }
+
+int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
+                   void* stream) {
+  GemmProblem g;
+  PI0_TRY(problem_from_desc(d, g));
+  const int rc = gemm_x3_launch(g, scratch_a, bytes_a, scratch_w, bytes_w, num_sms > 0 ? num_sms : 148, (cudaStream_t)stream);
+  PI0_REQUIRE(rc != 1, "pi0_gemm_f32x3: the problem does not fit the scratch buffers (A %zu, W %zu bytes needed) or N=%d is "
+              "not a multiple of 8", gemm_x3_operand_bytes((int64_t)g.nz0 * g.nz1, g.M, g.K),
+              gemm_x3_operand_bytes((int64_t)g.nz0 * g.nz1, g.N, g.K), g.N);
+  return rc;
+}
+
+size_t pi0_gemm_f32x3_scratch_bytes(int64_t nz, int64_t rows, int K) { return gemm_x3_operand_bytes(nz, rows, K); }
 
 int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream) {
   if (dtype == 1) return rmsnorm<float>((const float*)x, (float*)y, g, M, D, 1e-6f, 0, 0, 0, (cudaStream_t)stream);

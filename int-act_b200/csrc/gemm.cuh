@@ -36,6 +36,14 @@ inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64
 int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStream_t stream);
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream);
+// bf16 operands, epilogue and output in fp32 storage (EpiParams pointers are float buffers)
+int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream);
+// The fp32 regime's GEMM (gemm_x3.cu): fp32 operands split into three bf16 pieces each, six piece products accumulated in
+// fp32 on the tensor cores. scratch_a / scratch_w: caller-owned device buffers for the split operands. Returns 1 when the
+// problem does not fit the scratch or the tcgen05 constraints (caller falls back to the SIMT kernel), 0 on success, < 0 on error.
+int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
+                   cudaStream_t stream);
+size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K);
 // rank-4 bf16 tensor map {k, rows, z0, z1} with box {box_k, box_rows, 1, 1}, 64- or 128-byte swizzle, zero OOB fill
 int tc_make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0, int64_t sz1,
                 int box_rows, int box_k, int swizzle_bytes);

@@ -26,6 +26,7 @@ __device__ unsigned long long g_pair_timeline[2][16][4];  // [rank][tile][mma fi
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGroupM = 8;
+constexpr int kTcSegThreads = 384;  // gemm_tc_seg_kernel: warpgroup 0 (TMA, MMA, 2 idle warps) + 8 epilogue warps
 constexpr int kTcThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps (2 per TMEM lane quadrant)
 // TMA-store staging: every epilogue warp owns two 32-row x 64-byte (one 32-column bf16 chunk) buffers, written in the
 // 64-byte-swizzle pattern of the output tensor map (16-byte piece g of row r lands at piece g ^ ((r >> 1) & 3): the
@@ -383,6 +384,200 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   if (threadIdx.x == 32) PI0_STAMP(7);
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp32-output variant with SEGMENTED accumulation, for the split-bf16 GEMM of the fp32 regime (gemm_x3.cu).
+// The tensor core adds into its fp32 accumulator with truncation, so one accumulator run over a long K drifts towards zero
+// by ~2^-24 per MMA step (measured: mean relative error 1.8e-5 at K' = 6 x 16384 against 2e-6 for an fp32 FMA chain). Here
+// the MMA warp closes the TMEM accumulator every `seg_kb` k-blocks (the two accumulator buffers alternate, so the next
+// segment is issued while the previous one drains) and the epilogue warps add the segments into REGISTERS with round-to-
+// nearest fp32 adds: 4 chunks x 32 columns per thread. The fused epilogue then runs from the registers, in fp32 storage.
+// ---------------------------------------------------------------------------------------------
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kTcSegThreads, 1)
+gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
+                   const EpiParams ep, const int seg_kb) {
+  using Cfg = TcCfg<BN>;
+  constexpr bool kPaired = EPI == EPI_GEGLU || EPI == EPI_ROPE;
+  static_assert(!kPaired || BN == 256, "paired epilogues need one 256-wide tile");
+  constexpr int kChunks = BN / 32;                              // 32-column chunks of the tile
+  constexpr int kSlots = kPaired ? 4 : (kChunks + 1) / 2;       // chunks per epilogue warp (two warps share a lane quadrant)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + Cfg::kStages;
+  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull_bar[a], 1);
+      mbar_init(&tempty_bar[a], 8);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_k = (sh.K + kBK - 1) / kBK;
+  pdl_wait();
+
+  // 12 warps: warpgroup 0 = TMA warp, MMA warp and two idle warps, warpgroups 1-2 = the eight epilogue warps. A thread of a
+  // 384-thread CTA gets 168 registers, the epilogue needs 128 accumulators + a 32-column TMEM chunk: warpgroup 0 hands its
+  // registers over (128 x 88 + 256 x 208 = the 64512 the CTA was launched with).
+  // (the low-register group leaves through its own return so that the register bound of each side is unambiguous; the
+  // CTA-wide rendezvous before the TMEM release is a named barrier both sides arrive on)
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+        int z, tm, tn;
+        tile_coords(sh, idx, z, tm, tn);
+        const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
+          tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
+          tma_load_4d(sa + Cfg::kABytes, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+      for (int kb0 = 0; kb0 < num_k; kb0 += seg_kb) {
+        const int kb1 = min(num_k, kb0 + seg_kb);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+            const uint64_t da = umma_desc_k_sw128(sa);
+            const uint64_t db = umma_desc_k_sw128(sa + Cfg::kABytes);
+#pragma unroll
+            for (int k = 0; k < kBK / 16; ++k)
+              umma_bf16(tmem_d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+            umma_commit(&empty_bar[stage]);
+            if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  }
+  tc_fence_before();
+  asm volatile("bar.sync 2, %0;" ::"n"(kTcSegThreads) : "memory");
+  if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  return;
+  }
+
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+  {
+    const int quad = warp & 3;
+    const int part = (warp - 4) >> 2;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+      int z, tm, tn;
+      tile_coords(sh, idx, z, tm, tn);
+      const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+      const int row = tm * kBM + quad * 32 + lane;
+      const bool row_ok = row < sh.M;
+      const int n0 = tn * BN;
+      float r[kSlots][32];
+      // TMEM column offset of slot s inside the tile, -1 if this warp has no such chunk / it lies beyond N
+      auto slot_off = [&](int s) -> int {
+        if constexpr (kPaired) {
+          const int c = part * 2 + (s >> 1);      // pair index 0..3; halves of a pair are 128 columns apart
+          return (s & 1) * 128 + c * 32;
+        } else {
+          const int c = part * kSlots + s;
+          return (c < kChunks && n0 + c * 32 < sh.N) ? c * 32 : -1;
+        }
+      };
+      for (int kb0 = 0; kb0 < num_k; kb0 += seg_kb) {
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
+#pragma unroll
+        for (int s = 0; s < kSlots; ++s) {
+          const int off = slot_off(s);
+          if (off >= 0) {
+            float v[32];
+            tmem_ld_32x32(taddr + off, v);
+            tmem_ld_wait();
+            if (kb0 == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r[s][j] = v[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r[s][j] += v[j];
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+      if (row_ok) {
+        if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
+          const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
+#pragma unroll
+          for (int s = 0; s < kSlots; ++s) {
+            const int off = slot_off(s);
+            if (off >= 0) {
+              if constexpr (EPI == EPI_STORE) epi_store_chunk<float>(ep, row, n0 + off, sh.N, zoff, r[s]);
+              else epi_euler_chunk<float>(ep, row, n0 + off, sh.N, r[s]);
+            }
+          }
+        } else if constexpr (EPI == EPI_GEGLU) {
+          const int n_out = sh.N / 2;
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int out_col0 = tn * (BN / 2) + (part * 2 + i) * 32;
+            if (out_col0 < n_out) epi_geglu_chunk<float>(ep, row, out_col0, n_out, r[2 * i], r[2 * i + 1]);
+          }
+        } else {
+          const int which = tn < ep.n_q_heads ? 0 : (tn == ep.n_q_heads ? 1 : 2);
+#pragma unroll
+          for (int i = 0; i < 2; ++i) epi_rope_chunk<float>(ep, row, which, tn, part * 2 + i, r[2 * i], r[2 * i + 1]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  asm volatile("bar.sync 2, %0;" ::"n"(kTcSegThreads) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1077,6 +1272,71 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
       break;
   }
   set_error("gemm_tc: unsupported epilogue/tile combination epi=%d bn=%d", g.epi_mode, bn);
+  return -2;
+}
+
+
+// ---- bf16 operands, fp32 OUTPUT (the fp32 regime's split-bf16 GEMM, gemm_x3.cu): the single-CTA persistent kernel with the
+// epilogues instantiated for float storage and segmented accumulation (gemm_tc_seg_kernel). No split-K, no CTA pairs, no
+// TMA-store staging (fp32 rows are 128-byte lines per lane already). ----
+template <int BN, int EPI>
+static int launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  using Cfg = TcCfg<BN>;
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_seg_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)Cfg::kSmemBytes));
+    attr_once.mark();
+  }
+  CUtensorMap tmA, tmB;
+  const int a_rows = g.M < kBM ? ((g.M + 7) / 8) * 8 : kBM;
+  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, g.nz0, g.nz1, g.lda, g.a_z0, g.a_z1, a_rows));
+  PI0_TRY(make_map(&tmB, g.W, g.K, g.N, g.nz0, g.nz1, g.ldw, g.w_z0, g.w_z1, BN));
+  TcShape sh;
+  sh.M = g.M; sh.N = g.N; sh.K = g.K; sh.nz0 = g.nz0; sh.nz1 = g.nz1;
+  sh.tiles_m = (g.M + kBM - 1) / kBM;
+  sh.tiles_n = (g.N + BN - 1) / BN;
+  sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
+  set_super(sh, kBM);
+  sh.splits = 1;
+  sh.kb_per_split = (g.K + kBK - 1) / kBK;
+  sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
+  sh.tma_store = 0;
+  const int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
+  static int seg = getenv("PI0_X3_SEG_KB") ? atoi(getenv("PI0_X3_SEG_KB")) : 16;   // k-blocks (of 64) per accumulator run
+  PI0_CHECK_CUDA(launch_pdl(gemm_tc_seg_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcSegThreads), Cfg::kSmemBytes, stream, 1,
+                            tmA, tmB, sh, g.epi, seg > 0 ? seg : 1 << 30));
+  PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  return 0;
+}
+
+int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc (fp32 out): empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
+  int bn = g.bn;
+  if (g.epi_mode == EPI_STORE) {  // tile width by wave count: the widest tile that still gives every SM work
+    bn = 256;
+    const long tm = (g.M + kBM - 1) / kBM, nz = (long)g.nz0 * g.nz1;
+    while (bn > 32 && (g.N < bn || tm * ((g.N + bn - 1) / bn) * nz < num_sms)) bn >>= 1;
+  }
+  switch (g.epi_mode) {
+    case EPI_STORE:
+      switch (bn) {
+        case 256: return launch_f32out<256, EPI_STORE>(g, num_sms, stream);
+        case 128: return launch_f32out<128, EPI_STORE>(g, num_sms, stream);
+        case 64: return launch_f32out<64, EPI_STORE>(g, num_sms, stream);
+        default: return launch_f32out<32, EPI_STORE>(g, num_sms, stream);
+      }
+    case EPI_GEGLU:
+      PI0_REQUIRE(g.bn == 256 && g.N % 256 == 0, "gemm_tc (fp32 out): GeGLU expects bn=256 packing, N=%d", g.N);
+      return launch_f32out<256, EPI_GEGLU>(g, num_sms, stream);
+    case EPI_ROPE:
+      PI0_REQUIRE(g.N == (g.epi.n_q_heads + 2) * 256, "gemm_tc (fp32 out): RoPE epilogue expects N = (q_heads + 2) * 256");
+      return launch_f32out<256, EPI_ROPE>(g, num_sms, stream);
+    case EPI_EULER:
+      return launch_f32out<32, EPI_EULER>(g, num_sms, stream);
+  }
+  set_error("gemm_tc (fp32 out): unknown epilogue %d", g.epi_mode);
   return -2;
 }
 

@@ -82,10 +82,13 @@ struct pi0_ctx {
   int loop_pace_ns;  // PI0_LOOP_PACE (development knob)
   int loop_mode;  // 0 = off, 1 = per-step layers-only launches (PI0_MEGA=2), 2 = the whole Euler loop in one launch (default)
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
+  void* x3_a;  // fp32 regime: split-bf16 operand scratch of the tensor-core GEMM (gemm_x3.cu), null when it is off
+  void* x3_w;
+  size_t x3_a_bytes, x3_w_bytes;
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
   int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
-  Buf bufs[48];
+  Buf bufs[56];
   int nbufs;
   bool guarded;  // PI0_GUARD: 1 KiB 0xA5 zones behind every buffer
   // per-launch CUDA-event profiling (pi0_profile / pi0_profile_report); off on the product path
@@ -136,7 +139,7 @@ struct Carver {
     size_t o = off;
     off = round_up((int64_t)(off + bytes), 1024);
     if (guard) off += kGuardBytes;
-    if (ctx && ctx->nbufs < 48) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
+    if (ctx && ctx->nbufs < 56) ctx->bufs[ctx->nbufs++] = Buf{name, o, bytes};
     return base ? base + o : nullptr;
   }
 };
@@ -156,6 +159,13 @@ int validate_cfg(const pi0_model_cfg* c) {
   PI0_REQUIRE(c->n_gemma_layers >= 1 && c->n_gemma_layers <= PI0_GEMMA_LAYERS, "n_gemma_layers=%d",
               c->n_gemma_layers);
   return 0;
+}
+
+// fp32 regime (dtype 1): the GEMMs run on the tensor cores as split-bf16 products (gemm_x3.cu) unless PI0_FP32_GEMM=simt asks
+// for the CUDA-core check kernel
+bool fp32_x3_enabled() {
+  const char* e = getenv("PI0_FP32_GEMM");
+  return !(e && e[0] == 's');
 }
 
 void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
@@ -210,6 +220,21 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
   x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
   x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
+  x.x3_a = x.x3_w = nullptr;
+  x.x3_a_bytes = x.x3_w_bytes = 0;
+  if (cfg.dtype == 1 && fp32_x3_enabled()) {
+    // largest A-side operand: the prefix down projection [B * P, 16384] (the attention products, batched over heads, and
+    // the SigLIP MLP are smaller); largest W-side operand: the prefix gate/up weight [32768, 2048], or an activation used as
+    // W (K cache, V^T, SigLIP k / v^T of all heads) at large batches. A problem that does not fit falls back to the SIMT kernel.
+    const int64_t a_elems = std::max<int64_t>(std::max<int64_t>(Mg * kInter, Ms * (int64_t)(kVisInter + 8)),
+                                              std::max<int64_t>(B * P * kHeads * round_up(kvp, 8), B * kVisHeads * kPatches * (int64_t)kPatches));
+    const int64_t w_elems = std::max<int64_t>(std::max<int64_t>(2ll * kInter * kHidden, B * kVisHeads * kPatches * (int64_t)kPatches),
+                                              B * kHd * (int64_t)round_up(kvp, 8) * 2);
+    x.x3_a_bytes = (size_t)a_elems * 12;
+    x.x3_w_bytes = (size_t)w_elems * 12;
+    x.x3_a = cv.take("x3.a", x.x3_a_bytes);
+    x.x3_w = cv.take("x3.w", x.x3_w_bytes);
+  }
   if (c) {
     c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
     c->kv_pitch = kvp; c->sc_pitch = scp; c->vt_pitch = vtp; c->es = (int)es;
@@ -228,7 +253,12 @@ inline const void* at(const void* p, int64_t elems, int es) { return (const uint
 
 int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s) {
   PROF(label);
-  return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s);
+  const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
+  if (c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0) {
+    const int rc = gemm_x3_launch(g, c->x3_a, c->x3_a_bytes, c->x3_w, c->x3_w_bytes, sms, s);
+    if (rc != 1) return rc;   // 1: not eligible (ragged N with a bias, operand larger than the scratch) -> SIMT kernel
+  }
+  return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, sms, s);
 }
 
 int run_rmsnorm(pi0_ctx* c, const char* label, const void* x, void* y, const float* g, int M, int D, int rpb_in, int rpb_out, int off,
@@ -586,7 +616,9 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
   const bool bf = c->cfg.dtype == 0 && c->cfg.gemm_impl == 0;
   const int S = c->S, P = c->P, M = B * S;
   const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
-  const char* gemm = c->cfg.dtype == 1 || c->cfg.gemm_impl == 1 ? "simt_fp32_check" : "tcgen05";
+  const char* gemm = c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0
+                         ? "tcgen05_split_bf16x3_fp32"
+                         : (c->cfg.dtype == 1 || c->cfg.gemm_impl == 1 ? "simt_fp32_check" : "tcgen05");
   const char* siglip_attn = bf && c->siglip_fused ? (siglip_attention_use_tc() ? "fused_tcgen05" : "fused_mma_sync")
                                                   : "gemm_softmax_gemm";
   const bool pf = bf && c->prefill_fused && prefill_attention_supported(P, P) &&

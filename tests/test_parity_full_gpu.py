@@ -172,7 +172,7 @@ def test_path_report_names_the_variant_every_phase_takes(cuda):
     lib = Pi0Engine(packed, n_cams=2, horizon=16, max_batch=64).path_report(64)      # LIBERO shape: P = 584 > 336
     assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "gemm_softmax_gemm"
     f32 = Pi0Engine(PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.float32), dtype="fp32")
-    assert f32.path_report(1)["gemm"] == "simt_fp32_check"
+    assert f32.path_report(1)["gemm"] == "tcgen05_split_bf16x3_fp32"
 
 
 @pytest.mark.parametrize("B,n_cams,horizon,mega", [(1, 1, 4, 1), (1, 1, 4, 3), (3, 1, 4, 1), (6, 1, 4, 1), (16, 1, 4, 1),
