@@ -189,9 +189,10 @@ int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* str
  * split into three bf16 pieces (hi + mid + lo = the fp32 value exactly), the six piece products >= 2^-16 are one bf16 tcgen05
  * GEMM over K' = 6 K with fp32 accumulation and fp32 epilogues. Replaces torch.matmul / nn.Linear in fp32 (the reference with
  * `--use_bf16 False`, slurms/eval_scripts/simpler/ev_pi0_bridge_simpler.sh:99). scratch_a / scratch_w: device buffers of
- * pi0_gemm_f32x3_scratch_bytes(nz0 * nz1, M | N, K) bytes. */
-int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
-                   void* stream);
+ * pi0_gemm_f32x3_scratch_bytes(nz0 * nz1, M | N, K) bytes; scratch_p: optional fp32 workspace (any size, may be null) that
+ * lets skinny problems split K over the idle SMs (partials summed in split order by a second launch: deterministic). */
+int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* scratch_p,
+                   size_t bytes_p, int num_sms, void* stream);
 size_t pi0_gemm_f32x3_scratch_bytes(int64_t nz, int64_t rows, int K);
 
 int pi0_rmsnorm(const void* x, void* y, const float* g, int M, int D, int dtype, void* stream);

@@ -107,7 +107,7 @@ SIGNATURES = {
                                         C.c_int, c_ptr]),
     "pi0_decode_attention_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int,
                                              C.c_int, c_ptr]),
-    "pi0_gemm_f32x3": (C.c_int, [C.POINTER(GemmDesc), c_ptr, C.c_size_t, c_ptr, C.c_size_t, C.c_int, c_ptr]),
+    "pi0_gemm_f32x3": (C.c_int, [C.POINTER(GemmDesc), c_ptr, C.c_size_t, c_ptr, C.c_size_t, c_ptr, C.c_size_t, C.c_int, c_ptr]),
     "pi0_gemm_f32x3_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
     "pi0_decode_attention_split_static": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, C.c_int, c_ptr]),
@@ -171,7 +171,7 @@ def current_stream(device=None):
 def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bias=None, res=None, ldr=None,
          res_row_mod=0, act=ACT_NONE, alpha=1.0, post_div=0.0, post_mul=0.0, epi_mode=EPI_STORE, bn=128,
          nz0=1, nz1=1, a_z=(0, 0), w_z=(0, 0), out_z=(0, 0), dtype=DTYPE_BF16, impl=0, num_sms=148, splits=1,
-         **extra):
+         extra_partial_bytes=0, **extra):
     """Unit-test helper around pi0_gemm: out = A . W^T with the fused epilogue (A [M,K], W [N,K] row-major)."""
     d = GemmDesc()
     d.A, d.W, d.out = ptr(A), ptr(W), ptr(out)
@@ -202,7 +202,10 @@ def gemm(A, W, out, *, M=None, N=None, K=None, lda=None, ldw=None, ldc=None, bia
         bw = int(lib().pi0_gemm_f32x3_scratch_bytes(nz, d.N, d.K))
         sa = torch.empty(ba, dtype=torch.uint8, device=out.device)
         sw = torch.empty(bw, dtype=torch.uint8, device=out.device)
-        check(lib().pi0_gemm_f32x3(C.byref(d), ptr(sa), ba, ptr(sw), bw, num_sms, current_stream()), "pi0_gemm_f32x3")
+        bp = int(extra_partial_bytes)
+        sp = torch.empty(max(bp, 16), dtype=torch.uint8, device=out.device)
+        check(lib().pi0_gemm_f32x3(C.byref(d), ptr(sa), ba, ptr(sw), bw, ptr(sp) if bp else None, bp, num_sms,
+                                   current_stream()), "pi0_gemm_f32x3")
         torch.cuda.synchronize()   # the scratch tensors die with this frame
         return out
     check(lib().pi0_gemm(C.byref(d), dtype, impl, num_sms, current_stream()), "pi0_gemm")

@@ -48,11 +48,12 @@ int pi0_gemm(const pi0_gemm_desc* d, int dtype, int impl, int num_sms, void* str
   return gemm_launch(g, dtype, impl, num_sms, (cudaStream_t)stream);
 }
 
-int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
-                   void* stream) {
+int pi0_gemm_f32x3(const pi0_gemm_desc* d, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* scratch_p,
+                   size_t bytes_p, int num_sms, void* stream) {
   GemmProblem g;
   PI0_TRY(problem_from_desc(d, g));
-  const int rc = gemm_x3_launch(g, scratch_a, bytes_a, scratch_w, bytes_w, num_sms > 0 ? num_sms : 148, (cudaStream_t)stream);
+  const int rc = gemm_x3_launch(g, scratch_a, bytes_a, scratch_w, bytes_w, scratch_p, bytes_p, num_sms > 0 ? num_sms : 148,
+                                (cudaStream_t)stream);
   PI0_REQUIRE(rc != 1, "pi0_gemm_f32x3: the problem does not fit the scratch buffers (A %zu, W %zu bytes needed) or N=%d is "
               "not a multiple of 8", gemm_x3_operand_bytes((int64_t)g.nz0 * g.nz1, g.M, g.K),
               gemm_x3_operand_bytes((int64_t)g.nz0 * g.nz1, g.N, g.K), g.N);

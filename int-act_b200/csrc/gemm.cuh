@@ -37,13 +37,16 @@ int gemm_launch(const GemmProblem& g, int dtype, int impl, int num_sms, cudaStre
 
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream);
 // bf16 operands, epilogue and output in fp32 storage (EpiParams pointers are float buffers)
-int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream);
+// `partial`: optional fp32 workspace for the split-K form (skinny problems), may be null
+int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, void* partial, size_t partial_bytes, cudaStream_t stream);
 // The fp32 regime's GEMM (gemm_x3.cu): fp32 operands split into three bf16 pieces each, six piece products accumulated in
 // fp32 on the tensor cores. scratch_a / scratch_w: caller-owned device buffers for the split operands. Returns 1 when the
 // problem does not fit the scratch or the tcgen05 constraints (caller falls back to the SIMT kernel), 0 on success, < 0 on error.
-int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
-                   cudaStream_t stream);
+int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* partial,
+                   size_t bytes_p, int num_sms, cudaStream_t stream);
 size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K);
+// sums S fp32 partial slices [S][nz][M][ldp] in slice order and runs g's fused epilogue in fp32 storage (gemm_tc.cu)
+int gemm_f32_reduce_launch(const GemmProblem& g, const float* partial, int S, int ldp, cudaStream_t stream);
 // rank-4 bf16 tensor map {k, rows, z0, z1} with box {box_k, box_rows, 1, 1}, 64- or 128-byte swizzle, zero OOB fill
 int tc_make_map(CUtensorMap* map, const void* base, int K, int rows, int nz0, int nz1, int64_t ld, int64_t sz0, int64_t sz1,
                 int box_rows, int box_k, int swizzle_bytes);

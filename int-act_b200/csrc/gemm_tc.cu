@@ -397,7 +397,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kTcSegThreads, 1)
 gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
-                   const EpiParams ep, const int seg_kb) {
+                   const EpiParams ep, const int seg_kb, float* __restrict__ partial, const int ldp) {
   using Cfg = TcCfg<BN>;
   constexpr bool kPaired = EPI == EPI_GEGLU || EPI == EPI_ROPE;
   static_assert(!kPaired || BN == 256, "paired epilogues need one 256-wide tile");
@@ -433,6 +433,7 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int num_k = (sh.K + kBK - 1) / kBK;
+  const int total_items = sh.total_tiles * sh.splits;
   pdl_wait();
 
   // 12 warps: warpgroup 0 = TMA warp, MMA warp and two idle warps, warpgroups 1-2 = the eight epilogue warps. A thread of a
@@ -446,11 +447,12 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+      for (int idx = blockIdx.x; idx < total_items; idx += gridDim.x) {
         int z, tm, tn;
-        tile_coords(sh, idx, z, tm, tn);
+        tile_coords(sh, idx / sh.splits, z, tm, tn);
         const int z0 = z % sh.nz0, z1 = z / sh.nz0;
-        for (int kb = 0; kb < num_k; ++kb) {
+        const int kb_lo = (idx % sh.splits) * sh.kb_per_split, kb_hi = min(num_k, kb_lo + sh.kb_per_split);
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
@@ -466,9 +468,10 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
-      for (int kb0 = 0; kb0 < num_k; kb0 += seg_kb) {
-        const int kb1 = min(num_k, kb0 + seg_kb);
+    for (int idx = blockIdx.x; idx < total_items; idx += gridDim.x) {
+      const int kb_lo = (idx % sh.splits) * sh.kb_per_split, kb_hi = min(num_k, kb_lo + sh.kb_per_split);
+      for (int kb0 = kb_lo; kb0 < kb_hi; kb0 += seg_kb) {
+        const int kb1 = min(kb_hi, kb0 + seg_kb);
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -505,10 +508,12 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const int part = (warp - 4) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int idx = blockIdx.x; idx < sh.total_tiles; idx += gridDim.x) {
+    for (int idx = blockIdx.x; idx < total_items; idx += gridDim.x) {
       int z, tm, tn;
-      tile_coords(sh, idx, z, tm, tn);
+      tile_coords(sh, idx / sh.splits, z, tm, tn);
       const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+      const int sp = idx % sh.splits;
+      const int kb_lo = sp * sh.kb_per_split, kb_hi = min(num_k, kb_lo + sh.kb_per_split);
       const int row = tm * kBM + quad * 32 + lane;
       const bool row_ok = row < sh.M;
       const int n0 = tn * BN;
@@ -523,7 +528,7 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           return (c < kChunks && n0 + c * 32 < sh.N) ? c * 32 : -1;
         }
       };
-      for (int kb0 = 0; kb0 < num_k; kb0 += seg_kb) {
+      for (int kb0 = kb_lo; kb0 < kb_hi; kb0 += seg_kb) {
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
@@ -534,7 +539,7 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             float v[32];
             tmem_ld_32x32(taddr + off, v);
             tmem_ld_wait();
-            if (kb0 == 0) {
+            if (kb0 == kb_lo) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) r[s][j] = v[j];
             } else {
@@ -549,7 +554,22 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
-      if (row_ok) {
+      if (partial != nullptr) {
+        // split-K: this CTA's k-slice of the tile goes to the fp32 workspace [split][z][row][ldp]; x3_reduce_kernel sums the
+        // slices in split order and runs the epilogue
+        if (row_ok) {
+          float* prow = partial + (((int64_t)sp * (sh.nz0 * sh.nz1) + z) * sh.M + row) * ldp + n0;
+#pragma unroll
+          for (int s = 0; s < kSlots; ++s) {
+            const int off = slot_off(s);
+            if (off >= 0 && n0 + off < ldp) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(prow + off + j) = make_float4(r[s][j], r[s][j + 1], r[s][j + 2], r[s][j + 3]);
+            }
+          }
+        }
+      } else if (row_ok) {
         if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
           const int64_t zoff = (int64_t)z0 * ep.out_z0 + (int64_t)z1 * ep.out_z1;
 #pragma unroll
@@ -578,6 +598,83 @@ gemm_tc_seg_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 
   tc_fence_before();
   asm volatile("bar.sync 2, %0;" ::"n"(kTcSegThreads) : "memory");
+}
+
+
+// Second pass of the split-K forms (gemm_tc_seg_kernel, skinny_f32_kernel): v = sum over the k slices of the fp32 partials of
+// one (row, 32-column chunk [pair]), then the ordinary fused epilogue in fp32 storage. One WARP per unit: lane (g, f) loads
+// float4 f of the chunk from slices g, g + 4, g + 8, ... (all loads independent: one memory round trip whatever S is - a
+// thread-per-unit loop over S took 15 us at S = 16 with a few hundred threads in the grid), the four slice groups are combined
+// with shuffles in a fixed order (deterministic), and lane 0 runs the epilogue on the gathered 32 values.
+__device__ __forceinline__ void x3_fetch_chunk(const float* __restrict__ partial, int S, int64_t slice_stride, int64_t off,
+                                               int lane, float* v) {
+  const int g = lane >> 3, f = lane & 7;
+  float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+  const float* p = partial + off + f * 4;
+  for (int s0 = g; s0 < S; s0 += 16) {   // up to four independent loads per pass
+    float4 t[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int s = s0 + 4 * u;
+      t[u] = s < S ? __ldcg(reinterpret_cast<const float4*>(p + (int64_t)s * slice_stride)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w; }
+  }
+#pragma unroll
+  for (int sh = 16; sh >= 8; sh >>= 1) {
+    acc.x += __shfl_xor_sync(0xffffffffu, acc.x, sh);
+    acc.y += __shfl_xor_sync(0xffffffffu, acc.y, sh);
+    acc.z += __shfl_xor_sync(0xffffffffu, acc.z, sh);
+    acc.w += __shfl_xor_sync(0xffffffffu, acc.w, sh);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    v[4 * j] = __shfl_sync(0xffffffffu, acc.x, j);
+    v[4 * j + 1] = __shfl_sync(0xffffffffu, acc.y, j);
+    v[4 * j + 2] = __shfl_sync(0xffffffffu, acc.z, j);
+    v[4 * j + 3] = __shfl_sync(0xffffffffu, acc.w, j);
+  }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(256) x3_reduce_kernel(const float* __restrict__ partial, int S, int nz0, int nz1, int M,
+                                                        int N, int ldp, int units, const EpiParams ep) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t total = (int64_t)nz0 * nz1 * M * units;
+  const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (i >= total) return;
+  const int lane = threadIdx.x & 31;
+  const int row = (int)(i % M);
+  const int unit = (int)((i / M) % units);
+  const int z = (int)(i / ((int64_t)M * units));
+  const int64_t slice_stride = (int64_t)nz0 * nz1 * M * ldp;
+  const int64_t row_off = ((int64_t)z * M + row) * ldp;
+  float a[32];
+  if constexpr (EPI == EPI_STORE || EPI == EPI_EULER) {
+    const int col0 = unit * 32;
+    x3_fetch_chunk(partial, S, slice_stride, row_off + col0, lane, a);
+    if (lane == 0) {
+      if constexpr (EPI == EPI_STORE)
+        epi_store_chunk<float>(ep, row, col0, N, (int64_t)(z % nz0) * ep.out_z0 + (int64_t)(z / nz0) * ep.out_z1, a);
+      else epi_euler_chunk<float>(ep, row, col0, N, a);
+    }
+  } else if constexpr (EPI == EPI_GEGLU) {
+    float u[32];
+    const int out_col0 = unit * 32;                       // tile = 128 output columns: 128 gate rows then the 128 up rows
+    const int gcol = (out_col0 / 128) * 256 + out_col0 % 128;
+    x3_fetch_chunk(partial, S, slice_stride, row_off + gcol, lane, a);
+    x3_fetch_chunk(partial, S, slice_stride, row_off + gcol + 128, lane, u);
+    if (lane == 0) epi_geglu_chunk<float>(ep, row, out_col0, N / 2, a, u);
+  } else {
+    float x2[32];
+    const int head = unit >> 2, c = unit & 3;
+    x3_fetch_chunk(partial, S, slice_stride, row_off + head * 256 + c * 32, lane, a);
+    x3_fetch_chunk(partial, S, slice_stride, row_off + head * 256 + 128 + c * 32, lane, x2);
+    const int which = head < ep.n_q_heads ? 0 : (head == ep.n_q_heads ? 1 : 2);
+    if (lane == 0) epi_rope_chunk<float>(ep, row, which, head, c, a, x2);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1280,7 +1377,7 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
 // epilogues instantiated for float storage and segmented accumulation (gemm_tc_seg_kernel). No split-K, no CTA pairs, no
 // TMA-store staging (fp32 rows are 128-byte lines per lane already). ----
 template <int BN, int EPI>
-static int launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+static int launch_f32out(const GemmProblem& g, int num_sms, void* partial, size_t partial_bytes, cudaStream_t stream) {
   using Cfg = TcCfg<BN>;
   static PerDeviceOnce attr_once;
   if (attr_once.need()) {
@@ -1298,43 +1395,102 @@ static int launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream)
   sh.tiles_n = (g.N + BN - 1) / BN;
   sh.total_tiles = sh.tiles_m * sh.tiles_n * g.nz0 * g.nz1;
   set_super(sh, kBM);
+  const int num_k = (g.K + kBK - 1) / kBK;
   sh.splits = 1;
-  sh.kb_per_split = (g.K + kBK - 1) / kBK;
+  sh.kb_per_split = num_k;
   sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
   sh.tma_store = 0;
-  const int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
+  // split-K over CTAs when the tiles cover less than half of the SMs (denoise steps, batch-1 prefill): every CTA takes a
+  // k-slice of >= 4 k-blocks and leaves its fp32 partial in the workspace; x3_reduce_kernel finishes
+  const int ldp = (g.N + 31) / 32 * 32;
+  if (BN == 256 && partial != nullptr && sh.total_tiles * 2 <= num_sms && num_k >= 8) {
+    int want = num_sms / sh.total_tiles;
+    if (want > num_k / 4) want = num_k / 4;
+    const size_t per_split = (size_t)g.nz0 * g.nz1 * g.M * ldp * sizeof(float);
+    if ((size_t)want * per_split > partial_bytes) want = (int)(partial_bytes / per_split);
+    if (want > 1) {
+      const int per = (num_k + want - 1) / want;
+      sh.splits = (num_k + per - 1) / per;
+      sh.kb_per_split = per;
+    }
+  }
+  const int items = sh.total_tiles * sh.splits;
+  const int grid = items < num_sms ? items : num_sms;
   static int seg = getenv("PI0_X3_SEG_KB") ? atoi(getenv("PI0_X3_SEG_KB")) : 16;   // k-blocks (of 64) per accumulator run
+  float* part = sh.splits > 1 ? (float*)partial : nullptr;
   PI0_CHECK_CUDA(launch_pdl(gemm_tc_seg_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcSegThreads), Cfg::kSmemBytes, stream, 1,
-                            tmA, tmB, sh, g.epi, seg > 0 ? seg : 1 << 30));
+                            tmA, tmB, sh, g.epi, seg > 0 ? seg : 1 << 30, part, ldp));
   PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  if (sh.splits > 1) {
+    const int units = EPI == EPI_GEGLU ? g.N / 64 : EPI == EPI_ROPE ? (g.N / 256) * 4 : ldp / 32;
+    const int64_t warps = (int64_t)g.nz0 * g.nz1 * g.M * units;
+    PI0_CHECK_CUDA(launch_pdl(x3_reduce_kernel<EPI>, dim3((unsigned)((warps + 7) / 8)), dim3(256), 0, stream, 1,
+                              (const float*)partial, sh.splits, g.nz0, g.nz1, g.M, g.N, ldp, units, g.epi));
+    ++g_launch_count;
+  }
+  return 0;
+}
+
+// sums `S` fp32 partial slices [S][nz][M][ldp] in slice order and runs the fused epilogue of `g` in fp32 storage
+int gemm_f32_reduce_launch(const GemmProblem& g, const float* partial, int S, int ldp, cudaStream_t stream) {
+  const int units = g.epi_mode == EPI_GEGLU ? g.N / 64 : g.epi_mode == EPI_ROPE ? (g.N / 256) * 4 : ldp / 32;
+  const int64_t warps = (int64_t)g.nz0 * g.nz1 * g.M * units;
+  const dim3 grid((unsigned)((warps + 7) / 8));
+  switch (g.epi_mode) {
+    case EPI_STORE:
+      PI0_CHECK_CUDA(launch_pdl(x3_reduce_kernel<EPI_STORE>, grid, dim3(256), 0, stream, 1, partial, S, g.nz0, g.nz1, g.M, g.N,
+                                ldp, units, g.epi));
+      break;
+    case EPI_GEGLU:
+      PI0_CHECK_CUDA(launch_pdl(x3_reduce_kernel<EPI_GEGLU>, grid, dim3(256), 0, stream, 1, partial, S, g.nz0, g.nz1, g.M, g.N,
+                                ldp, units, g.epi));
+      break;
+    case EPI_ROPE:
+      PI0_CHECK_CUDA(launch_pdl(x3_reduce_kernel<EPI_ROPE>, grid, dim3(256), 0, stream, 1, partial, S, g.nz0, g.nz1, g.M, g.N,
+                                ldp, units, g.epi));
+      break;
+    case EPI_EULER:
+      PI0_CHECK_CUDA(launch_pdl(x3_reduce_kernel<EPI_EULER>, grid, dim3(256), 0, stream, 1, partial, S, g.nz0, g.nz1, g.M, g.N,
+                                ldp, units, g.epi));
+      break;
+    default:
+      set_error("gemm_f32_reduce: unknown epilogue %d", g.epi_mode);
+      return -2;
+  }
   ++g_launch_count;
   return 0;
 }
 
-int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, void* partial, size_t partial_bytes, cudaStream_t stream) {
   PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc (fp32 out): empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
   int bn = g.bn;
-  if (g.epi_mode == EPI_STORE) {  // tile width by wave count: the widest tile that still gives every SM work
-    bn = 256;
+  if (g.epi_mode == EPI_STORE) {
     const long tm = (g.M + kBM - 1) / kBM, nz = (long)g.nz0 * g.nz1;
-    while (bn > 32 && (g.N < bn || tm * ((g.N + bn - 1) / bn) * nz < num_sms)) bn >>= 1;
+    const long t256 = tm * ((g.N + 255) / 256) * nz;
+    if (partial != nullptr && g.N >= 256 && t256 * 2 <= num_sms && g.K >= 8 * kBK) {
+      bn = 256;   // few wide tiles, the k range split over the idle SMs
+    } else {      // tile width by wave count: the widest tile that still gives every SM work
+      bn = 256;
+      while (bn > 32 && (g.N < bn || tm * ((g.N + bn - 1) / bn) * nz < num_sms)) bn >>= 1;
+    }
   }
   switch (g.epi_mode) {
     case EPI_STORE:
       switch (bn) {
-        case 256: return launch_f32out<256, EPI_STORE>(g, num_sms, stream);
-        case 128: return launch_f32out<128, EPI_STORE>(g, num_sms, stream);
-        case 64: return launch_f32out<64, EPI_STORE>(g, num_sms, stream);
-        default: return launch_f32out<32, EPI_STORE>(g, num_sms, stream);
+        case 256: return launch_f32out<256, EPI_STORE>(g, num_sms, partial, partial_bytes, stream);
+        case 128: return launch_f32out<128, EPI_STORE>(g, num_sms, partial, partial_bytes, stream);
+        case 64: return launch_f32out<64, EPI_STORE>(g, num_sms, partial, partial_bytes, stream);
+        default: return launch_f32out<32, EPI_STORE>(g, num_sms, partial, partial_bytes, stream);
       }
     case EPI_GEGLU:
       PI0_REQUIRE(g.bn == 256 && g.N % 256 == 0, "gemm_tc (fp32 out): GeGLU expects bn=256 packing, N=%d", g.N);
-      return launch_f32out<256, EPI_GEGLU>(g, num_sms, stream);
+      return launch_f32out<256, EPI_GEGLU>(g, num_sms, partial, partial_bytes, stream);
     case EPI_ROPE:
       PI0_REQUIRE(g.N == (g.epi.n_q_heads + 2) * 256, "gemm_tc (fp32 out): RoPE epilogue expects N = (q_heads + 2) * 256");
-      return launch_f32out<256, EPI_ROPE>(g, num_sms, stream);
+      return launch_f32out<256, EPI_ROPE>(g, num_sms, partial, partial_bytes, stream);
     case EPI_EULER:
-      return launch_f32out<32, EPI_EULER>(g, num_sms, stream);
+      return launch_f32out<32, EPI_EULER>(g, num_sms, partial, partial_bytes, stream);
   }
   set_error("gemm_tc (fp32 out): unknown epilogue %d", g.epi_mode);
   return -2;

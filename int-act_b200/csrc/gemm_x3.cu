@@ -94,6 +94,105 @@ int launch_split(const void* src, int64_t ld, int64_t sz0, int64_t sz1, int nz0,
   return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Skinny problems of the fp32 regime (M <= 64 rows: the denoise steps up to batch 12): the weight matrix is read ONCE, in
+// fp32, by CUDA-core FMAs - at M = 40 the tensor-core form above spends 4 launches and a 16-byte-per-parameter split pass
+// on a problem whose floor is one pass over 4 bytes per parameter. Work item = (64 output columns, 256-wide k slice): the
+// CTA stages the A slice [M x 256] and the W slice [64 x 256] in shared memory with cp.async, thread (col, q) accumulates
+// rows q, q + 4, ... with 16-byte shared loads (A broadcast across the warp, W conflict-free through a 260-float pitch),
+// and the k slices' partial sums go to the fp32 workspace that x3_reduce_kernel (gemm_tc.cu) sums in slice order before
+// the fused epilogue. Deterministic, plain fp32 arithmetic.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSkCols = 64, kSkK = 256, kSkWPitch = kSkK + 4, kSkMaxM = 64;
+
+// RPT = rows per thread = ceil(M / 4), a template parameter: predicated-off FMAs still take issue slots (the 16-row form took
+// 23 us at M = 5)
+template <int RPT>
+__global__ void __launch_bounds__(256) skinny_f32_kernel(const float* __restrict__ A, int64_t lda,
+                                                         const float* __restrict__ W, int64_t ldw, int M, int N,
+                                                         float* __restrict__ partial, int ldp) {
+  extern __shared__ __align__(16) float sk_smem[];
+  float* Ws = sk_smem;                         // [64][260]
+  float* As = sk_smem + kSkCols * kSkWPitch;   // [M][256]
+  pdl_trigger();
+  const int cb = blockIdx.x, ks = blockIdx.y;
+  const int col = threadIdx.x & 63, q = threadIdx.x >> 6;
+  // the weights are never written by a preceding kernel: their slice is requested before the dependency wait
+  for (int i = threadIdx.x; i < kSkCols * (kSkK / 4); i += 256) {
+    const int c = i / (kSkK / 4), k4 = i % (kSkK / 4);
+    const float* src = W + (int64_t)(cb * kSkCols + c) * ldw + ks * kSkK + k4 * 4;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(Ws + c * kSkWPitch + k4 * 4)), "l"(src) : "memory");
+  }
+  pdl_wait();
+  for (int i = threadIdx.x; i < M * (kSkK / 4); i += 256) {
+    const int r = i / (kSkK / 4), k4 = i % (kSkK / 4);
+    const float* src = A + (int64_t)r * lda + ks * kSkK + k4 * 4;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(As + r * kSkK + k4 * 4)), "l"(src) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  const int nr = (M - q + 3) / 4;   // rows q, q + 4, ... < M
+  float acc[RPT];
+#pragma unroll
+  for (int i = 0; i < RPT; ++i) acc[i] = 0.0f;
+  const float4* wrow = reinterpret_cast<const float4*>(Ws + col * kSkWPitch);
+#pragma unroll 2
+  for (int k4 = 0; k4 < kSkK / 4; ++k4) {
+    const float4 w = wrow[k4];
+#pragma unroll
+    for (int i = 0; i < RPT; ++i) {
+      if (i < nr) {
+        const float4 a = *reinterpret_cast<const float4*>(As + (q + 4 * i) * kSkK + k4 * 4);
+        acc[i] = fmaf(a.x, w.x, acc[i]);
+        acc[i] = fmaf(a.y, w.y, acc[i]);
+        acc[i] = fmaf(a.z, w.z, acc[i]);
+        acc[i] = fmaf(a.w, w.w, acc[i]);
+      }
+    }
+  }
+  float* dst = partial + ((int64_t)ks * M) * ldp + cb * kSkCols + col;
+#pragma unroll
+  for (int i = 0; i < RPT; ++i)
+    if (i < nr) dst[(int64_t)(q + 4 * i) * ldp] = acc[i];
+}
+
+// 0 = launched, 1 = not a skinny problem / does not fit
+int skinny_f32_launch(const GemmProblem& g, void* partial, size_t bytes_p, cudaStream_t stream) {
+  static const bool off = getenv("PI0_FP32_SKINNY") && getenv("PI0_FP32_SKINNY")[0] == '0';
+  if (off || partial == nullptr || g.nz0 * g.nz1 != 1 || g.M > kSkMaxM || g.N % kSkCols != 0 || g.K % kSkK != 0) return 1;
+  if (g.lda % 4 != 0 || g.ldw % 4 != 0 || ((reinterpret_cast<uintptr_t>(g.A) | reinterpret_cast<uintptr_t>(g.W)) & 15) != 0)
+    return 1;
+  const int S = g.K / kSkK, ldp = (g.N + 31) / 32 * 32;
+  if ((size_t)S * g.M * ldp * sizeof(float) > bytes_p) return 1;
+  const size_t smem = (size_t)(kSkCols * kSkWPitch + g.M * kSkK) * sizeof(float);
+  const int max_smem = (int)((kSkCols * kSkWPitch + kSkMaxM * kSkK) * sizeof(float));
+  const dim3 grid((unsigned)(g.N / kSkCols), (unsigned)S);
+  const int rpt = (g.M + 3) / 4;
+#define PI0_SKINNY_CASE(R)                                                                                              \
+  {                                                                                                                     \
+    static PerDeviceOnce once;                                                                                          \
+    if (once.need()) {                                                                                                  \
+      PI0_CHECK_CUDA(cudaFuncSetAttribute(skinny_f32_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
+      once.mark();                                                                                                      \
+    }                                                                                                                   \
+    PI0_CHECK_CUDA(launch_pdl(skinny_f32_kernel<R>, grid, dim3(256), smem, stream, 1, (const float*)g.A, g.lda,         \
+                              (const float*)g.W, g.ldw, g.M, g.N, (float*)partial, ldp));                               \
+  }
+  if (rpt <= 1) PI0_SKINNY_CASE(1)
+  else if (rpt <= 2) PI0_SKINNY_CASE(2)
+  else if (rpt <= 4) PI0_SKINNY_CASE(4)
+  else if (rpt <= 6) PI0_SKINNY_CASE(6)
+  else if (rpt <= 8) PI0_SKINNY_CASE(8)
+  else if (rpt <= 10) PI0_SKINNY_CASE(10)
+  else if (rpt <= 12) PI0_SKINNY_CASE(12)
+  else PI0_SKINNY_CASE(16)
+#undef PI0_SKINNY_CASE
+  ++g_launch_count;
+  return gemm_f32_reduce_launch(g, (const float*)partial, S, ldp, stream);
+}
+
 }  // namespace
 
 size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K) {
@@ -101,10 +200,14 @@ size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K) {
   return (size_t)(nz * rows * kPieces * Kp * 2);
 }
 
-int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, int num_sms,
-                   cudaStream_t stream) {
+int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* partial,
+                   size_t bytes_p, int num_sms, cudaStream_t stream) {
   PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_x3: empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
   const int64_t nz = (int64_t)g.nz0 * g.nz1;
+  {
+    const int rc = skinny_f32_launch(g, partial, bytes_p, stream);
+    if (rc != 1) return rc;
+  }
   // what the tcgen05 launcher needs from the epilogue side (the SIMT kernel has no such constraints)
   const bool ragged_ok = g.epi_mode == EPI_STORE && g.epi.bias == nullptr && g.epi.res == nullptr &&
                          g.epi.ldc >= (int64_t)((g.N + 7) / 8) * 8;
@@ -120,7 +223,7 @@ int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* 
   t.W = scratch_w; t.ldw = K6; t.w_z0 = (int64_t)g.N * K6; t.w_z1 = (int64_t)g.nz0 * g.N * K6;
   PI0_REQUIRE(K6 <= 0x7fffffff, "gemm_x3: K=%d too long", g.K);
   t.K = (int)K6;
-  return gemm_tc_launch_f32out(t, num_sms, stream);
+  return gemm_tc_launch_f32out(t, num_sms, partial, bytes_p, stream);
 }
 
 }  // namespace pi0

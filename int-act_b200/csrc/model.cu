@@ -84,7 +84,8 @@ struct pi0_ctx {
   bool siglip_fused;  // fused SigLIP attention kernel (PI0_SIGLIP_FUSED=0 disables)
   void* x3_a;  // fp32 regime: split-bf16 operand scratch of the tensor-core GEMM (gemm_x3.cu), null when it is off
   void* x3_w;
-  size_t x3_a_bytes, x3_w_bytes;
+  void* x3_p;  // fp32 partial sums of the split-K form (skinny problems)
+  size_t x3_a_bytes, x3_w_bytes, x3_p_bytes;
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
   int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
@@ -220,8 +221,8 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
   x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
   x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
-  x.x3_a = x.x3_w = nullptr;
-  x.x3_a_bytes = x.x3_w_bytes = 0;
+  x.x3_a = x.x3_w = x.x3_p = nullptr;
+  x.x3_a_bytes = x.x3_w_bytes = x.x3_p_bytes = 0;
   if (cfg.dtype == 1 && fp32_x3_enabled()) {
     // largest A-side operand: the prefix down projection [B * P, 16384] (the attention products, batched over heads, and
     // the SigLIP MLP are smaller); largest W-side operand: the prefix gate/up weight [32768, 2048], or an activation used as
@@ -234,6 +235,8 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
     x.x3_w_bytes = (size_t)w_elems * 12;
     x.x3_a = cv.take("x3.a", x.x3_a_bytes);
     x.x3_w = cv.take("x3.w", x.x3_w_bytes);
+    x.x3_p_bytes = (size_t)64 << 20;
+    x.x3_p = cv.take("x3.partial", x.x3_p_bytes);
   }
   if (c) {
     c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
@@ -255,7 +258,7 @@ int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s
   PROF(label);
   const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
   if (c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0) {
-    const int rc = gemm_x3_launch(g, c->x3_a, c->x3_a_bytes, c->x3_w, c->x3_w_bytes, sms, s);
+    const int rc = gemm_x3_launch(g, c->x3_a, c->x3_a_bytes, c->x3_w, c->x3_w_bytes, c->x3_p, c->x3_p_bytes, sms, s);
     if (rc != 1) return rc;   // 1: not eligible (ragged N with a bias, operand larger than the scratch) -> SIMT kernel
   }
   return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, sms, s);

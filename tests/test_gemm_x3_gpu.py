@@ -29,6 +29,39 @@ def test_x3_plain_matches_fp64(cuda, M, N, K):
     assert err <= 2e-5, err
 
 
+@pytest.mark.parametrize("M,N,K", [(40, 1024, 4096), (5, 2560, 1024), (328, 2048, 2048), (16, 520, 16384)])
+def test_x3_split_k_over_idle_sms_matches_fp64(cuda, M, N, K):
+    """Skinny problems (denoise steps, batch-1 prefill): with a partial-sum workspace every CTA takes a k-slice and a second
+    launch sums the slices in split order and runs the epilogue (bias + residual here)."""
+    A = _rand((M, K), cuda, seed=21)
+    W = _rand((N, K), cuda, K ** -0.5, seed=22)
+    bias = _rand((N,), cuda, 0.1, seed=23)
+    res = _rand((M, N), cuda, seed=24)
+    outs = []
+    for pbytes in (64 << 20, 0):
+        out = torch.full((M, N), float("nan"), device=cuda)
+        pb.gemm(A, W, out, bias=bias, res=res, dtype=pb.DTYPE_F32, impl="x3", bn=256, extra_partial_bytes=pbytes)
+        outs.append(out)
+    ref = A.double() @ W.double().t() + bias.double() + res.double()
+    assert (outs[0].double() - ref).abs().max().item() <= 2e-5
+    assert (outs[0] - outs[1]).abs().max().item() <= 1e-5      # split and unsplit forms agree to fp32 summation order
+    again = torch.zeros((M, N), device=cuda)
+    pb.gemm(A, W, again, bias=bias, res=res, dtype=pb.DTYPE_F32, impl="x3", bn=256, extra_partial_bytes=64 << 20)
+    assert torch.equal(again, outs[0])                          # deterministic
+
+
+def test_x3_geglu_split_k(cuda):
+    M, K, inter = 40, 1024, 1024
+    A = _rand((M, K), cuda, seed=12)
+    Wg = _rand((inter, K), cuda, 0.03, seed=13)
+    Wu = _rand((inter, K), cuda, 0.03, seed=14)
+    Wgu = torch.stack([Wg.view(-1, 128, K), Wu.view(-1, 128, K)], dim=1).reshape(2 * inter, K).contiguous()
+    out = torch.zeros((M, inter), device=cuda)
+    pb.gemm(A, Wgu, out, epi_mode=pb.EPI_GEGLU, bn=256, dtype=pb.DTYPE_F32, impl="x3", extra_partial_bytes=64 << 20)
+    ref = torch.nn.functional.gelu(A.double() @ Wg.double().t(), approximate="tanh") * (A.double() @ Wu.double().t())
+    assert (out.double() - ref).abs().max().item() <= 1e-4
+
+
 def test_x3_split_is_exact_for_fp32_inputs_with_24_significant_bits(cuda):
     """hi + mid + lo reproduces every fp32 value: with a one-hot W the GEMM must return A bit for bit (every dropped piece
     product is zero then)."""
@@ -102,5 +135,5 @@ def test_x3_rejects_a_problem_larger_than_its_scratch(cuda):
     d.vt_col0 = 0x7FFFFFFF
     d.vt_hd = d.vt_heads = d.vt_rpb = 1
     small = torch.empty(1024, dtype=torch.uint8, device=cuda)
-    rc = pb.lib().pi0_gemm_f32x3(C.byref(d), pb.ptr(small), 1024, pb.ptr(small), 1024, 148, pb.current_stream())
+    rc = pb.lib().pi0_gemm_f32x3(C.byref(d), pb.ptr(small), 1024, pb.ptr(small), 1024, None, 0, 148, pb.current_stream())
     assert rc == -2 and "scratch" in pb.lib().pi0_last_error().decode()

@@ -23,7 +23,7 @@ def timed(fn, n=5):
     return a.elapsed_time(b) / n
 
 
-for M, N, K in [(328, 2048, 2048), (2624, 2048, 16384), (2624, 32768, 2048), (2048, 1152, 4304), (320, 1024, 4096),
+for M, N, K in [(40, 1024, 4096), (40, 8192, 1024), (5, 2560, 1024), (328, 2048, 2048), (2624, 2048, 16384), (2624, 32768, 2048), (2048, 1152, 4304), (320, 1024, 4096),
                 (20992, 2048, 16384)]:
     g = torch.Generator(device=dev).manual_seed(M + N + K)
     A = torch.randn((M, K), generator=g, device=dev)
@@ -42,9 +42,11 @@ for M, N, K in [(328, 2048, 2048), (2624, 2048, 16384), (2624, 32768, 2048), (20
     bw = int(pb.lib().pi0_gemm_f32x3_scratch_bytes(1, N, K))
     sa = torch.empty(ba, dtype=torch.uint8, device=dev)
     sw = torch.empty(bw, dtype=torch.uint8, device=dev)
+    bp = 64 << 20
+    sp = torch.empty(bp, dtype=torch.uint8, device=dev)
 
     def x3():
-        pb.check(pb.lib().pi0_gemm_f32x3(C.byref(d), pb.ptr(sa), ba, pb.ptr(sw), bw, 148, pb.current_stream()), "x3")
+        pb.check(pb.lib().pi0_gemm_f32x3(C.byref(d), pb.ptr(sa), ba, pb.ptr(sw), bw, pb.ptr(sp), bp, 148, pb.current_stream()), "x3")
     t_x3 = timed(x3)
     e_x3 = (out[:256].double() - ref).abs().max().item()
     r_x3 = ((out[:256].double() - ref).abs().mean() / ref.abs().mean()).item()
