@@ -235,6 +235,13 @@ int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream);
  * Replaces eager_attention_forward of the prefix pass ([mirror] src/model/mvla/mllm.py:265-317). */
 int pi0_prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B,
                           int T, int P, int kv_pitch, int vt_pitch, int num_sms, void* stream);
+/* The same attention for LONG key ranges (csrc/attn_long.cu, tcgen05, keys in blocks of 256, two passes: row max / sum, then
+ * probabilities and P.V): up to 1024 keys. n_suffix == 0: prefix pass, T query tokens against the P prefix keys (pad mask).
+ * n_suffix > 0: denoise-step suffix attention, T == n_suffix suffix tokens against P + n_suffix keys (pad mask + cumsum rule,
+ * cum i32 [n_suffix]). Replaces eager_attention_forward ([mirror] src/model/mvla/mllm.py:265-317) for the LIBERO (P = 584,
+ * 17 suffix tokens) and 3-camera (P = 840) shapes that exceed pi0_prefill_attention / pi0_decode_attention_batch. P % 8 == 0. */
+int pi0_attention_long(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, const int32_t* cum,
+                       int B, int T, int P, int n_suffix, int kv_pitch, int vt_pitch, int num_sms, void* stream);
 int pi0_position_ids(const uint8_t* pad, int B, int P, int S, int32_t* prefix_pos, int32_t* suffix_pos, void* stream);
 
 

@@ -109,6 +109,8 @@ SIGNATURES = {
                                              C.c_int, c_ptr]),
     "pi0_gemm_f32x3": (C.c_int, [C.POINTER(GemmDesc), c_ptr, C.c_size_t, c_ptr, C.c_size_t, c_ptr, C.c_size_t, C.c_int, c_ptr]),
     "pi0_gemm_f32x3_scratch_bytes": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int]),
+    "pi0_attention_long": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, C.c_int, c_ptr]),
     "pi0_decode_attention_split_static": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, C.c_int, c_ptr]),
     "pi0_decode_attention_split_static_max_bytes": (C.c_longlong, []),

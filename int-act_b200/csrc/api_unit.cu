@@ -92,6 +92,12 @@ int pi0_prefill_attention(const void* q, const void* kcache, const void* vtcache
                            (cudaStream_t)stream);
 }
 
+int pi0_attention_long(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, const int32_t* cum,
+                       int B, int T, int P, int n_suffix, int kv_pitch, int vt_pitch, int num_sms, void* stream) {
+  return attention_long(q, kcache, vtcache, att, pad, cum, B, T, P, n_suffix, kv_pitch, vt_pitch, num_sms > 0 ? num_sms : 148,
+                        (cudaStream_t)stream);
+}
+
 int pi0_siglip_attention(const void* qkv, void* att, int B, void* stream) {
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -41,6 +41,10 @@ int siglip_attention_mma(const void* qkv, void* att, int B, cudaStream_t s);
 int siglip_attention_tc(const void* qkv, void* att, int B, int num_sms, cudaStream_t s);
 bool siglip_attention_use_tc();
 // fused prefix-prefill attention on tcgen05 (attn_prefill.cu); q / att [B*T][8*256], P <= 336 prefix keys
+// long key ranges (<= 1024 keys), prefix pass (n_suffix == 0) or denoise-step suffix attention (attn_long.cu)
+bool attention_long_supported(int T, int P, int n_suffix);
+int attention_long(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, const int* cum, int B,
+                   int T, int P, int n_suffix, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);
 bool prefill_attention_supported(int T, int P);
 int prefill_attention(const void* q, const void* kcache, const void* vtcache, void* att, const uint8_t* pad, int B, int T,
                       int P, int kv_pitch, int vt_pitch, int num_sms, cudaStream_t s);

@@ -254,6 +254,26 @@ __global__ void suffix_cum_kernel(int* cum, int S) {
 inline void* at(void* p, int64_t elems, int es) { return (uint8_t*)p + elems * es; }
 inline const void* at(const void* p, int64_t elems, int es) { return (const uint8_t*)p + elems * es; }
 
+// The long-key tcgen05 attention (attn_long.cu) takes over where the one-tile kernels stop (P > 336 in the prefix pass; more
+// than 6 suffix tokens or more than 352 keys in the denoise step) once a launch has enough (sample, 128-row tile) items to
+// occupy the GPU; PI0_ATTN_LONG=0 disables, PI0_ATTN_LONG_MIN_ITEMS overrides the threshold (default 16).
+bool attn_long_enabled() {
+  const char* e = getenv("PI0_ATTN_LONG");
+  return !(e && e[0] == '0');
+}
+int attn_long_min_items() {
+  const char* e = getenv("PI0_ATTN_LONG_MIN_ITEMS");
+  return e ? atoi(e) : 16;
+}
+bool use_long_suffix(const pi0_ctx* c, int B) {
+  return attn_long_enabled() && attention_long_supported(c->S, c->P, c->S) &&
+         (int64_t)B * ((c->S * 8 + 127) / 128) >= attn_long_min_items();
+}
+bool use_long_prefix(const pi0_ctx* c, int B, int T) {
+  return attn_long_enabled() && c->prefill_fused && !prefill_attention_supported(T, c->P) &&
+         attention_long_supported(T, c->P, 0) && (int64_t)B * ((T * 8 + 127) / 128) >= c->prefill_fused_min_tiles;
+}
+
 int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s) {
   PROF(label);
   const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
@@ -374,9 +394,22 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     else if (B >= 4 && c->attn_split && decode_attention_split_supported(c->S, c->P))
       PI0_TRY(decode_attention_split(q, kc, vt, att, c->sc_e, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch,
                                      c->vt_pitch, s));
+    else if (use_long_suffix(c, B))
+      // long horizons / multi-camera prefixes (LIBERO: 17 suffix tokens over 601 keys): tcgen05, keys in blocks of 256
+      PI0_TRY(attention_long(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->S, c->kv_pitch, c->vt_pitch,
+                             c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
     else
       PI0_TRY(decode_attention(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch,
                                c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+  } else if (suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && use_long_suffix(c, B)) {
+    PROF("denoise.attention");
+    PI0_TRY(attention_long(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->S, c->kv_pitch, c->vt_pitch,
+                           c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+  } else if (!suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && use_long_prefix(c, B, T)) {
+    // prefix pass beyond 336 keys (LIBERO P = 584, 3 cameras P = 840): the two-pass tcgen05 kernel of attn_long.cu
+    PROF("prefill.attention");
+    PI0_TRY(attention_long(q, kc, vt, att, c->pad, nullptr, B, T, c->P, 0, c->kv_pitch, c->vt_pitch,
+                           c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
   } else if (!suffix && c->prefill_fused && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 &&
              prefill_attention_supported(T, c->P) &&
              (int64_t)B * ((T * kHeads + 127) / 128) >= c->prefill_fused_min_tiles) {
@@ -626,7 +659,7 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
                                                   : "gemm_softmax_gemm";
   const bool pf = bf && c->prefill_fused && prefill_attention_supported(P, P) &&
                   (int64_t)B * ((P * kHeads + 127) / 128) >= c->prefill_fused_min_tiles;
-  const char* prefill_attn = pf ? "fused_tcgen05" : "gemm_softmax_gemm";
+  const char* prefill_attn = pf ? "fused_tcgen05" : (bf && use_long_prefix(c, B, P) ? "fused_tcgen05_long" : "gemm_softmax_gemm");
   const char* denoise;
   const char* denoise_attn;
   if (c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(M, S, P, c->mega_ctas)) {
@@ -646,9 +679,10 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
     if (bf && S <= 48 && P + S <= 640) {
       if (B > 12 && c->attn_split && decode_attention_batch_supported(S, P)) denoise_attn = "batch_cta_pair_per_sample";
       else if (B >= 4 && c->attn_split && decode_attention_split_supported(S, P)) denoise_attn = "split_two_launches";
+      else if (use_long_suffix(c, B)) denoise_attn = "fused_tcgen05_long";
       else denoise_attn = "fused_single_cta";
     } else {
-      denoise_attn = "gemm_softmax_gemm";
+      denoise_attn = bf && use_long_suffix(c, B) ? "fused_tcgen05_long" : "gemm_softmax_gemm";
     }
   }
   char tmp[640];

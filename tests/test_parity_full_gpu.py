@@ -79,6 +79,29 @@ def test_full_depth_other_baseline_shapes(cuda, name, n_cams, lang_len, horizon,
     assert err <= 1e-2, err
 
 
+@pytest.mark.parametrize("n_cams,horizon,B,n_valid", [(2, 16, 3, [72, 9, 40]), (3, 50, 2, [72, 30])])
+def test_long_key_attention_kernel_in_the_engine(cuda, monkeypatch, n_cams, horizon, B, n_valid):
+    """LIBERO (P = 584, 17 suffix tokens) and 3-camera / 50-step (P = 840, 51 suffix tokens) shapes with the long-key tcgen05
+    attention forced on at a small batch (it is picked from 16 (sample, tile) items on): against the oracle and against the
+    fallback chain it replaces."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=3, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=3)
+    inp = synthetic_inputs(B, n_cams, 72, horizon, dims.vocab, n_valid)
+    monkeypatch.setenv("PI0_ATTN_LONG_MIN_ITEMS", "1")
+    monkeypatch.setenv("PI0_PREFILL_FUSED_MIN_TILES", "1")
+    eng, out = _engine_out(cuda, sd, "bf16", B, inp, n_cams, 72, horizon, graph=False)
+    rep = eng.path_report(B)
+    assert rep["prefill_attention"] == "fused_tcgen05_long" and rep["denoise_attention"] == "fused_tcgen05_long", rep
+    monkeypatch.setenv("PI0_ATTN_LONG", "0")
+    eng2, out2 = _engine_out(cuda, sd, "bf16", B, inp, n_cams, 72, horizon, graph=False)
+    assert eng2.path_report(B)["prefill_attention"] == "gemm_softmax_gemm"
+    ref = oracle_for(sd, dims, n_cams, 72, horizon, "bf16").sample_actions(*inp)
+    err, dif = (out - ref).abs().max().item(), (out - out2).abs().max().item()
+    print(f"\n[long attention n_cams={n_cams} H={horizon}] vs oracle {err:.3e}; vs fallback chain {dif:.3e}")
+    assert err <= 1e-2, err
+    assert dif <= 1e-2, dif
+
+
 def test_state_row_and_vacuity_guards(cuda):
     """Zeroing the state moves the action by only ~1e-2 (the tolerance), so a broken state_proj path could hide behind the
     action check: the state row of the suffix embedding is compared directly."""
@@ -170,7 +193,8 @@ def test_path_report_names_the_variant_every_phase_takes(cuda):
     assert b64["denoise"] == "tcgen05_per_op" and b64["denoise_attention"] == "batch_cta_pair_per_sample"
     assert b64["prefill_attention"] == "fused_tcgen05" and b64["siglip_attention"] == "fused_tcgen05"
     lib = Pi0Engine(packed, n_cams=2, horizon=16, max_batch=64).path_report(64)      # LIBERO shape: P = 584 > 336
-    assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "gemm_softmax_gemm"
+    assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "fused_tcgen05_long"
+    assert lib["denoise_attention"] == "fused_tcgen05_long"
     f32 = Pi0Engine(PackedWeights(random_state_dict(dims, device=cuda, seed=0), cuda, torch.float32), dtype="fp32")
     assert f32.path_report(1)["gemm"] == "tcgen05_split_bf16x3_fp32"
 
