@@ -269,9 +269,15 @@ bool use_long_suffix(const pi0_ctx* c, int B) {
   return attn_long_enabled() && attention_long_supported(c->S, c->P, c->S) &&
          (int64_t)B * ((c->S * 8 + 127) / 128) >= attn_long_min_items();
 }
+// prefix pass: the blocked two-pass kernel also beats the one-tile kernel at the shapes that one covers (bridge P = 328:
+// 156 vs 174 us per launch at batch 64, tools/prefill_attn_compare.py), so it takes every prefix pass with at least
+// PI0_ATTN_LONG_PREFIX_MIN_ITEMS (sample, tile) items (default 128, about one item per SM: at batch 1 - 21 items of ~20 us - the
+// three-launch scores -> softmax -> P.V chain, which spreads the work over every SM, stays faster: 9.32 vs 9.49 ms end to end;
+// at batch 4 the two are equal)
 bool use_long_prefix(const pi0_ctx* c, int B, int T) {
-  return attn_long_enabled() && c->prefill_fused && !prefill_attention_supported(T, c->P) &&
-         attention_long_supported(T, c->P, 0) && (int64_t)B * ((T * 8 + 127) / 128) >= c->prefill_fused_min_tiles;
+  const int min_items = getenv("PI0_ATTN_LONG_PREFIX_MIN_ITEMS") ? atoi(getenv("PI0_ATTN_LONG_PREFIX_MIN_ITEMS")) : 128;
+  return attn_long_enabled() && c->prefill_fused && attention_long_supported(T, c->P, 0) &&
+         (int64_t)B * ((T * 8 + 127) / 128) >= min_items;
 }
 
 int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s) {
@@ -406,7 +412,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     PI0_TRY(attention_long(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->S, c->kv_pitch, c->vt_pitch,
                            c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
   } else if (!suffix && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0 && use_long_prefix(c, B, T)) {
-    // prefix pass beyond 336 keys (LIBERO P = 584, 3 cameras P = 840): the two-pass tcgen05 kernel of attn_long.cu
+    // prefix pass, rollout batches: the blocked two-pass tcgen05 kernel of attn_long.cu (any P up to 1024)
     PROF("prefill.attention");
     PI0_TRY(attention_long(q, kc, vt, att, c->pad, nullptr, B, T, c->P, 0, c->kv_pitch, c->vt_pitch,
                            c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
@@ -659,7 +665,7 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
                                                   : "gemm_softmax_gemm";
   const bool pf = bf && c->prefill_fused && prefill_attention_supported(P, P) &&
                   (int64_t)B * ((P * kHeads + 127) / 128) >= c->prefill_fused_min_tiles;
-  const char* prefill_attn = pf ? "fused_tcgen05" : (bf && use_long_prefix(c, B, P) ? "fused_tcgen05_long" : "gemm_softmax_gemm");
+  const char* prefill_attn = bf && use_long_prefix(c, B, P) ? "fused_tcgen05_long" : (pf ? "fused_tcgen05" : "gemm_softmax_gemm");
   const char* denoise;
   const char* denoise_attn;
   if (c->loop_mode > 0 && c->mega_ctas > 0 && loop_supported(M, S, P, c->mega_ctas)) {
@@ -675,7 +681,7 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
     denoise = "skinny_mma_sync_per_op";
     denoise_attn = "fused_single_cta";
   } else {
-    denoise = bf ? "tcgen05_per_op" : "simt_fp32_check";
+    denoise = bf ? "tcgen05_per_op" : (c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0 ? "fp32_per_op" : "simt_fp32_check");
     if (bf && S <= 48 && P + S <= 640) {
       if (B > 12 && c->attn_split && decode_attention_batch_supported(S, P)) denoise_attn = "batch_cta_pair_per_sample";
       else if (B >= 4 && c->attn_split && decode_attention_split_supported(S, P)) denoise_attn = "split_two_launches";

@@ -88,7 +88,7 @@ def test_long_key_attention_kernel_in_the_engine(cuda, monkeypatch, n_cams, hori
     sd = random_state_dict(dims, device=cuda, seed=3)
     inp = synthetic_inputs(B, n_cams, 72, horizon, dims.vocab, n_valid)
     monkeypatch.setenv("PI0_ATTN_LONG_MIN_ITEMS", "1")
-    monkeypatch.setenv("PI0_PREFILL_FUSED_MIN_TILES", "1")
+    monkeypatch.setenv("PI0_ATTN_LONG_PREFIX_MIN_ITEMS", "1")
     eng, out = _engine_out(cuda, sd, "bf16", B, inp, n_cams, 72, horizon, graph=False)
     rep = eng.path_report(B)
     assert rep["prefill_attention"] == "fused_tcgen05_long" and rep["denoise_attention"] == "fused_tcgen05_long", rep
@@ -191,7 +191,7 @@ def test_path_report_names_the_variant_every_phase_takes(cuda):
     b1, b64 = eng.path_report(1), eng.path_report(64)
     assert b1["denoise"] == "persistent_layers_kernel_per_step" and b1["prefill_attention"] == "gemm_softmax_gemm"
     assert b64["denoise"] == "tcgen05_per_op" and b64["denoise_attention"] == "batch_cta_pair_per_sample"
-    assert b64["prefill_attention"] == "fused_tcgen05" and b64["siglip_attention"] == "fused_tcgen05"
+    assert b64["prefill_attention"] == "fused_tcgen05_long" and b64["siglip_attention"] == "fused_tcgen05"
     lib = Pi0Engine(packed, n_cams=2, horizon=16, max_batch=64).path_report(64)      # LIBERO shape: P = 584 > 336
     assert lib["prefix_tokens"] == 584 and lib["prefill_attention"] == "fused_tcgen05_long"
     assert lib["denoise_attention"] == "fused_tcgen05_long"
