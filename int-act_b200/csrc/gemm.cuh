@@ -42,8 +42,19 @@ int gemm_tc_launch_f32out(const GemmProblem& g, int num_sms, void* partial, size
 // The fp32 regime's GEMM (gemm_x3.cu): fp32 operands split into three bf16 pieces each, six piece products accumulated in
 // fp32 on the tensor cores. scratch_a / scratch_w: caller-owned device buffers for the split operands. Returns 1 when the
 // problem does not fit the scratch or the tcgen05 constraints (caller falls back to the SIMT kernel), 0 on success, < 0 on error.
+// Optional cache of split WEIGHT operands (12 bytes per parameter, caller-owned memory): a weight is split the first time a GEMM
+// uses it and found by its pointer afterwards, which removes the W-side split pass from every later call.
+struct X3WeightCache {
+  uint8_t* base = nullptr;
+  size_t bytes = 0, used = 0;
+  static constexpr int kMaxEntries = 1024;
+  const void* key[kMaxEntries];
+  size_t off[kMaxEntries];
+  int n = 0;
+};
+// w_is_weight: g.W is a constant parameter matrix (not an activation), i.e. eligible for `cache`
 int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* partial,
-                   size_t bytes_p, int num_sms, cudaStream_t stream);
+                   size_t bytes_p, int num_sms, cudaStream_t stream, X3WeightCache* cache = nullptr, bool w_is_weight = false);
 size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K);
 // sums S fp32 partial slices [S][nz][M][ldp] in slice order and runs g's fused epilogue in fp32 storage (gemm_tc.cu)
 int gemm_f32_reduce_launch(const GemmProblem& g, const float* partial, int S, int ldp, cudaStream_t stream);

@@ -10,8 +10,8 @@
 //     A' = [ lo | hi | mid | mid | hi  | hi ]        W' = [ hi | lo | mid | hi  | mid | hi ]
 // (small terms first, so they meet a small accumulator), which the unchanged tcgen05 pipeline of gemm_tc.cu runs with the
 // epilogues instantiated for fp32 storage: 6 bf16 MMAs per fp32 FMA is still >5x the CUDA-core peak.
-// The split operands go to caller-owned scratch (the ctx workspace); weights are split on every call (no 12-byte-per-
-// parameter copy is kept), which costs one memory-bound pass per GEMM.
+// The split operands go to caller-owned scratch (the ctx workspace). Weights are split on their first use into an optional
+// cache (X3WeightCache, 12 bytes per parameter) and found by pointer afterwards; without it they are split on every call.
 #include "gemm.cuh"
 
 namespace pi0 {
@@ -201,7 +201,7 @@ size_t gemm_x3_operand_bytes(int64_t nz, int64_t rows, int K) {
 }
 
 int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* scratch_w, size_t bytes_w, void* partial,
-                   size_t bytes_p, int num_sms, cudaStream_t stream) {
+                   size_t bytes_p, int num_sms, cudaStream_t stream, X3WeightCache* cache, bool w_is_weight) {
   PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_x3: empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
   const int64_t nz = (int64_t)g.nz0 * g.nz1;
   {
@@ -213,14 +213,33 @@ int gemm_x3_launch(const GemmProblem& g, void* scratch_a, size_t bytes_a, void* 
                          g.epi.ldc >= (int64_t)((g.N + 7) / 8) * 8;
   if (!(g.N % 8 == 0 || g.epi_mode == EPI_EULER || g.epi.vt != nullptr || ragged_ok)) return 1;
   if (scratch_a == nullptr || scratch_w == nullptr) return 1;
-  if (gemm_x3_operand_bytes(nz, g.M, g.K) > bytes_a || gemm_x3_operand_bytes(nz, g.N, g.K) > bytes_w) return 1;
+  const size_t w_bytes = gemm_x3_operand_bytes(nz, g.N, g.K);
+  if (gemm_x3_operand_bytes(nz, g.M, g.K) > bytes_a) return 1;
   const int Kp = (g.K + 7) / 8 * 8;
+  // W side: a cached split of a weight, a fresh cache entry, or the per-call scratch
+  void* w_split = nullptr;
+  bool w_ready = false;
+  if (cache != nullptr && w_is_weight && nz == 1 && cache->base != nullptr) {
+    for (int i = 0; i < cache->n; ++i)
+      if (cache->key[i] == g.W) { w_split = cache->base + cache->off[i]; w_ready = true; break; }
+    if (!w_ready && cache->n < X3WeightCache::kMaxEntries && cache->used + w_bytes <= cache->bytes) {
+      w_split = cache->base + cache->used;
+      cache->key[cache->n] = g.W;
+      cache->off[cache->n] = cache->used;
+      ++cache->n;
+      cache->used += (w_bytes + 1023) & ~(size_t)1023;
+    }
+  }
+  if (w_split == nullptr) {
+    if (w_bytes > bytes_w) return 1;
+    w_split = scratch_w;
+  }
   PI0_TRY(launch_split<false>(g.A, g.lda, g.a_z0, g.a_z1, g.nz0, g.nz1, g.M, g.K, Kp, scratch_a, num_sms, stream));
-  PI0_TRY(launch_split<true>(g.W, g.ldw, g.w_z0, g.w_z1, g.nz0, g.nz1, g.N, g.K, Kp, scratch_w, num_sms, stream));
+  if (!w_ready) PI0_TRY(launch_split<true>(g.W, g.ldw, g.w_z0, g.w_z1, g.nz0, g.nz1, g.N, g.K, Kp, w_split, num_sms, stream));
   GemmProblem t = g;
   const int64_t K6 = (int64_t)kPieces * Kp;
   t.A = scratch_a; t.lda = K6; t.a_z0 = (int64_t)g.M * K6; t.a_z1 = (int64_t)g.nz0 * g.M * K6;
-  t.W = scratch_w; t.ldw = K6; t.w_z0 = (int64_t)g.N * K6; t.w_z1 = (int64_t)g.nz0 * g.N * K6;
+  t.W = w_split; t.ldw = K6; t.w_z0 = (int64_t)g.N * K6; t.w_z1 = (int64_t)g.nz0 * g.N * K6;
   PI0_REQUIRE(K6 <= 0x7fffffff, "gemm_x3: K=%d too long", g.K);
   t.K = (int)K6;
   return gemm_tc_launch_f32out(t, num_sms, partial, bytes_p, stream);

@@ -86,6 +86,7 @@ struct pi0_ctx {
   void* x3_w;
   void* x3_p;  // fp32 partial sums of the split-K form (skinny problems)
   size_t x3_a_bytes, x3_w_bytes, x3_p_bytes;
+  X3WeightCache x3_cache;  // split copies of the GEMM weights (PI0_FP32_WCACHE=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
   int prefill_fused_min_tiles;  // ... for at least this many 128-row tiles (PI0_PREFILL_FUSED_MIN_TILES, default 2 x SMs)
@@ -237,6 +238,19 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
     x.x3_w = cv.take("x3.w", x.x3_w_bytes);
     x.x3_p_bytes = (size_t)64 << 20;
     x.x3_p = cv.take("x3.partial", x.x3_p_bytes);
+    const char* wc = getenv("PI0_FP32_WCACHE");
+    if (!(wc && wc[0] == '0')) {
+      // 12 bytes per GEMM weight element: SigLIP layers + patch embedding + projector, Gemma layers, expert layers + heads
+      const int64_t sig = (int64_t)cfg.n_siglip_layers * ((int64_t)3 * kVisHidden * kVisHidden + (int64_t)kVisHidden * kVisHidden +
+                                                          2ll * kVisInter * kVisHidden) +
+                          (int64_t)kVisHidden * kPatchK + (int64_t)kHidden * kVisHidden;
+      const int64_t gem = (int64_t)NL * ((int64_t)(kHeads + 2) * kHd * kHidden + (int64_t)kHidden * kHidden + 3ll * kInter * kHidden);
+      const int64_t exp_ = (int64_t)NL * ((int64_t)(kHeads + 2) * kHd * kExpHidden + (int64_t)kExpHidden * kHidden +
+                                          3ll * kExpInter * kExpHidden) + (8ll << 20);
+      const size_t cache_bytes = (size_t)(sig + gem + exp_) * 12 + ((size_t)1024 << 10);
+      uint8_t* cb = (uint8_t*)cv.take("x3.wcache", cache_bytes);
+      if (c) { c->x3_cache.base = cb; c->x3_cache.bytes = cache_bytes; c->x3_cache.used = 0; c->x3_cache.n = 0; }
+    }
   }
   if (c) {
     c->P = P; c->S = S; c->H = H; c->L = cfg.lang_len; c->ncam = cfg.n_cams; c->maxB = (int)B;
@@ -284,7 +298,11 @@ int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s
   PROF(label);
   const int sms = c->cfg.num_sms > 0 ? c->cfg.num_sms : 148;
   if (c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0) {
-    const int rc = gemm_x3_launch(g, c->x3_a, c->x3_a_bytes, c->x3_w, c->x3_w_bytes, c->x3_p, c->x3_p_bytes, sms, s);
+    // W is a weight iff it lies outside the workspace (activations used as W - K cache, V^T, SigLIP k / v^T - live inside)
+    const uint8_t* wp = (const uint8_t*)g.W;
+    const bool is_weight = wp < c->base || wp >= c->base + c->ws_bytes;
+    const int rc = gemm_x3_launch(g, c->x3_a, c->x3_a_bytes, c->x3_w, c->x3_w_bytes, c->x3_p, c->x3_p_bytes, sms, s,
+                                  &c->x3_cache, is_weight);
     if (rc != 1) return rc;   // 1: not eligible (ragged N with a bias, operand larger than the scratch) -> SIMT kernel
   }
   return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, sms, s);
