@@ -689,7 +689,7 @@ def b200_arm(args, rank, world, local_rank):
             ge["speedup_b1_latency"] = ge["p50_b1_ms"] / p50
             line["gpu_eager"] = ge
         if args.fp32_regime and world == 1:
-            line["fp32_regime"] = time_fp32_regime(args.workload, dev)
+            line["fp32_regime"] = time_fp32_regime(args.workload, dev, B=args.fp32_batch)
 
         # ---- (5) CPU baseline on the host cores (N=1 only) --------------------------------------------------------
         if world == 1 and not args.no_cpu_baseline:
@@ -717,6 +717,7 @@ def main():
     ap.add_argument("--no-gpu-eager", action="store_true")
     ap.add_argument("--fp32-regime", action="store_true",
                     help="also time the --use_bf16 False regime (SIMT fp32 path) next to PyTorch eager fp32")
+    ap.add_argument("--fp32-batch", type=int, default=8, help="rollout batch of the --fp32-regime leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the C3-strong / C4 / C5 side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
