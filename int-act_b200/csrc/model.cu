@@ -413,7 +413,12 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     PROF("denoise.attention");
     // rollout batches: two wide launches up to B = 12 (latency-bound regime), one CTA pair per sample with K / V^T staged
     // in shared memory above (bandwidth-bound regime); the one-CTA-per-(sample, head group) kernel otherwise
-    if (B > 12 && c->attn_split && decode_attention_batch_supported(c->S, c->P))
+    if (B > 96 && use_long_suffix(c, B))
+      // more samples than ~2/3 of the SMs: the blocked tcgen05 kernel (one item per sample here) passes the batch kernel
+      // (two CTAs per sample): 21.3 vs 24.3 us at B = 128, 38.4 vs 48.1 us at B = 256 (tools/suffix_attn_compare.py)
+      PI0_TRY(attention_long(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->S, c->kv_pitch, c->vt_pitch,
+                             c->cfg.num_sms > 0 ? c->cfg.num_sms : 148, s));
+    else if (B > 12 && c->attn_split && decode_attention_batch_supported(c->S, c->P))
       PI0_TRY(decode_attention_batch(q, kc, vt, att, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch, c->vt_pitch, s));
     else if (B >= 4 && c->attn_split && decode_attention_split_supported(c->S, c->P))
       PI0_TRY(decode_attention_split(q, kc, vt, att, c->sc_e, c->pad, c->suffix_cum, B, c->S, c->P, c->kv_pitch,
@@ -701,7 +706,8 @@ int pi0_path_report(pi0_ctx* c, int B, char* buf, size_t buf_bytes) {
   } else {
     denoise = bf ? "tcgen05_per_op" : (c->cfg.dtype == 1 && c->x3_a != nullptr && c->cfg.gemm_impl == 0 ? "fp32_per_op" : "simt_fp32_check");
     if (bf && S <= 48 && P + S <= 640) {
-      if (B > 12 && c->attn_split && decode_attention_batch_supported(S, P)) denoise_attn = "batch_cta_pair_per_sample";
+      if (B > 96 && use_long_suffix(c, B)) denoise_attn = "fused_tcgen05_long";
+      else if (B > 12 && c->attn_split && decode_attention_batch_supported(S, P)) denoise_attn = "batch_cta_pair_per_sample";
       else if (B >= 4 && c->attn_split && decode_attention_split_supported(S, P)) denoise_attn = "split_two_launches";
       else if (use_long_suffix(c, B)) denoise_attn = "fused_tcgen05_long";
       else denoise_attn = "fused_single_cta";
