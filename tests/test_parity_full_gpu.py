@@ -102,6 +102,21 @@ def test_long_key_attention_kernel_in_the_engine(cuda, monkeypatch, n_cams, hori
     assert dif <= 1e-2, dif
 
 
+def test_batch_above_96_takes_the_blocked_attention_kernel_in_the_denoise_step(cuda):
+    """Bridge shape, 100 observations per GPU (C4 runs 256): the denoise attention switches from the batch kernel to the blocked
+    tcgen05 kernel; rows 0, 50, 99 against the oracle."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=4)
+    B = 100
+    inp = synthetic_inputs(B, vocab=dims.vocab, n_valid_text=[72, 9, 33, 2, 50, 17, 64])
+    eng, out = _engine_out(cuda, sd, "bf16", B, inp, graph=False)
+    assert eng.path_report(B)["denoise_attention"] == "fused_tcgen05_long"
+    rows = [0, 50, 99]
+    ref = oracle_for(sd, dims, 1, 72, 4, "bf16").sample_actions(*_subset(inp, rows))
+    err = (out[rows] - ref).abs().max().item()
+    assert err <= 1e-2, err
+
+
 def test_state_row_and_vacuity_guards(cuda):
     """Zeroing the state moves the action by only ~1e-2 (the tolerance), so a broken state_proj path could hide behind the
     action check: the state row of the suffix embedding is compared directly."""
