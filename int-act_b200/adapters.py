@@ -232,15 +232,21 @@ class BridgeSimplerBatchAdapter(_GpuAdapterBase):
         return {"observation.images.top": images, "observation.state": state, "task": obs["task"]}
 
 
-    def preprocess_many(self, obs_list) -> dict:
-        """Several requests (each a [b_i, H, W, 3] frame stack) as ONE host concatenation, one H2D copy and one resize /
-        proprio launch - the coalescing server's path. Same arithmetic per observation as `preprocess`."""
+    @staticmethod
+    def gather_many(obs_list) -> dict:
+        """HOST half of `preprocess_many`: several requests (each a [b_i, H, W, 3] frame stack) concatenated into one
+        observation dict. Touches no GPU state, so the server can run it for the next group while the current one computes."""
         frames = np.concatenate([np.asarray(o["observation.images.top"]) for o in obs_list], axis=0)
         eef = np.concatenate([np.asarray(o["observation.state"], dtype=np.float32).reshape(-1, 8) for o in obs_list], axis=0)
         tasks = [t for o in obs_list for t in ([o["task"]] if isinstance(o["task"], str) else list(o["task"]))]
         if frames.shape[0] != eef.shape[0] or frames.shape[0] != len(tasks):
             raise ValueError("frames / states / tasks disagree on the number of observations")
-        return self.preprocess({"observation.images.top": frames, "observation.state": eef, "task": tasks})
+        return {"observation.images.top": frames, "observation.state": eef, "task": tasks}
+
+    def preprocess_many(self, obs_list) -> dict:
+        """Several requests as ONE host concatenation, one H2D copy and one resize / proprio launch - the coalescing server's
+        path. Same arithmetic per observation as `preprocess`."""
+        return self.preprocess(self.gather_many(obs_list))
 
 
 class BridgeSimplerAdapter(_GpuAdapterBase):

@@ -49,6 +49,7 @@ def build_server(argv: List[str]):
     server = WebsocketPolicyServer(policy=wrappers[0], host=cfg.eval_cfg.host, port=cfg.eval_cfg.port,
                                    metadata={"model": "pi0", "action_step": cfg.eval_cfg.action_step},
                                    max_batch=max_batch, batch_window_ms=float(srv.get("batch_window_ms", 0.0)),
+                                   workers_per_replica=int(srv.get("workers_per_replica", 1)),
                                    replicas=wrappers[1:])
     model_path = srv.get("model_path")
     if model_path:

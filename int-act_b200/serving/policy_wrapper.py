@@ -19,6 +19,7 @@ processing stay per request, so every client gets exactly the adapter output it 
 from __future__ import annotations
 
 import gc
+import threading
 import random
 from typing import Callable, List, Optional
 
@@ -68,6 +69,9 @@ class LeRobotPolicyWrapper:
         self._model_loader = model_loader
         self._adapter_factory = adapter_factory
         self.max_batch = max_batch
+        # the engine's static buffers and the adapter's device state belong to one caller at a time; host-side work (gathering a
+        # group's frames) happens outside this lock, so a second server worker can prepare the next group meanwhile
+        self._gpu_lock = threading.RLock()
         if pipeline_cfg is not None:
             if model_class is None:
                 raise ValueError("pipeline_cfg given without model_class")
@@ -153,11 +157,12 @@ class LeRobotPolicyWrapper:
 
     def select_action(self, element: dict):
         self._require_model()
-        element = self.env_adapter.preprocess(element)
-        with torch.inference_mode():
-            actions = torch.stack([self.model.select_action(element) for _ in range(self.action_step)], dim=1)
-        actions = actions[0] if actions.shape[0] == 1 else actions  # no batch dim for a single observation
-        return self.env_adapter.postprocess(actions.float())
+        with self._gpu_lock:
+            element = self.env_adapter.preprocess(element)
+            with torch.inference_mode():
+                actions = torch.stack([self.model.select_action(element) for _ in range(self.action_step)], dim=1)
+            actions = actions[0] if actions.shape[0] == 1 else actions  # no batch dim for a single observation
+            return self.env_adapter.postprocess(actions.float())
 
     def can_batch(self) -> bool:
         """Requests may share an engine batch when every request consumes one whole chunk (no stale queue entries,
@@ -174,9 +179,26 @@ class LeRobotPolicyWrapper:
         self._require_model()
         if len(elements) == 1 or not self.can_batch():
             return [self.select_action(e) for e in elements]
+        pre, failed, batch, host = [], {}, None, None
+        if hasattr(self.env_adapter, "gather_many"):
+            try:  # one host concatenation for the whole group, outside the GPU lock; any problem -> per-request path
+                sizes = [int(np.asarray(e["observation.state"]).reshape(-1, 8).shape[0]) for e in elements]
+                host = self.env_adapter.gather_many(elements)
+            except Exception:  # noqa: BLE001
+                host = None
+        with self._gpu_lock:
+            return self._run_many_locked(elements, host, sizes if host is not None else None)
+
+    def _run_many_locked(self, elements, host, sizes):
         pre, failed, batch = [], {}, None
-        if hasattr(self.env_adapter, "preprocess_many"):
-            try:  # one host concatenation + one H2D + one kernel for the whole group; any problem -> per-request path
+        if host is not None:
+            try:  # one H2D + one resize / proprio launch for the whole group
+                batch = self.env_adapter.preprocess(host)
+                pre = [(i, None) for i in range(len(elements))]
+            except Exception:  # noqa: BLE001
+                batch, pre = None, []
+        elif hasattr(self.env_adapter, "preprocess_many"):
+            try:
                 sizes = [int(np.asarray(e["observation.state"]).reshape(-1, 8).shape[0]) for e in elements]
                 batch = self.env_adapter.preprocess_many(elements)
                 pre = [(i, None) for i in range(len(elements))]

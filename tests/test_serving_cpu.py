@@ -141,6 +141,26 @@ def test_concurrent_requests_are_batched_and_routed():
         assert pol1.groups == [1, 1, 1]
 
 
+def test_two_workers_per_replica_route_every_request_and_keep_control_barriers():
+    """workers_per_replica=2: two threads share the one policy (host gathering of the next group overlaps the GPU part of the
+    current one); every client still gets its own answer and a reset is still a barrier."""
+    pol = FakePolicy()
+    n = 10
+    with ServerThread(pol, max_batch=4, batch_window_ms=50.0, workers_per_replica=2) as srv:
+        clients = [WebsocketPolicyClient("127.0.0.1", srv.bound_port) for _ in range(n)]
+        out = [None] * n
+        for rnd in range(2):
+            ts = [threading.Thread(target=lambda i=i: out.__setitem__(i, clients[i].infer(obs_for(float(i + rnd)))))
+                  for i in range(n)]
+            [t.start() for t in ts]
+            [t.join(20) for t in ts]
+            for i in range(n):
+                assert np.all(out[i] == float(i + rnd)), (i, out[i])
+            assert clients[0].reset() == {"status": "reset"}
+        assert sum(pol.groups) == 2 * n and srv.stats["requests"] == 2 * n
+        [c.close() for c in clients]
+
+
 @pytest.mark.skipif(not os.path.isdir(REF_PKG), reason="reference tree not mounted")
 def test_reference_client_talks_to_this_server():
     sys.path.insert(0, REF_PKG)

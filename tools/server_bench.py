@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=torch.cuda.device_count())
     ap.add_argument("--clients", type=int, default=64)
     ap.add_argument("--max-batch", type=int, default=32)
+    ap.add_argument("--workers", type=int, default=1, help="server worker threads per replica")
     ap.add_argument("--window-ms", type=float, default=2.0)
     ap.add_argument("--seconds", type=float, default=10.0)
     a = ap.parse_args()
@@ -44,7 +45,7 @@ def main():
         pol._state_dict = None
         del sd
         wrappers.append(w)
-    server = WebsocketPolicyServer(wrappers[0], host="127.0.0.1", port=0, metadata={}, max_batch=a.max_batch,
+    server = WebsocketPolicyServer(wrappers[0], host="127.0.0.1", port=0, metadata={}, max_batch=a.max_batch, workers_per_replica=a.workers,
                                    batch_window_ms=a.window_ms, replicas=wrappers[1:])
     ready, holder = threading.Event(), {}
 
