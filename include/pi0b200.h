@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PI0_ABI_VERSION 3
+#define PI0_ABI_VERSION 4
 
 #define PI0_SIGLIP_LAYERS 27
 #define PI0_GEMMA_LAYERS 18
@@ -180,6 +180,13 @@ typedef struct pi0_gemm_desc {
   void* kcache; int32_t n_q_heads; int64_t kv_pitch;
   float dt;
   int32_t splits;    /* split-K factor = thread-block cluster size, 1..8; 0 = pick from the shape */
+  /* ABI 4. Producer side (epi_mode 0): rowsq_out[row * rowsq_ld + col / 32] = sum of squares of the stored values of every
+   * 32-column chunk. Consumer side (epi_mode 1 / 2, bn 256, bf16): GemmaRMSNorm fused into the A operand - A is the RAW
+   * residual stream, a <- rnd((a * rstd[row]) * norm_gain[k]) in shared memory before the MMA, rstd[row] = rsqrt(sum of
+   * norm_rowsq[row * norm_slots + 0 .. norm_slots) / K + norm_eps). Replaces GemmaRMSNorm + Linear
+   * ([mirror] src/model/mvla/mllm.py:30-53,206-215). */
+  float* rowsq_out; int32_t rowsq_ld;
+  const float* norm_gain; const float* norm_rowsq; int32_t norm_slots; float norm_eps;
 } pi0_gemm_desc;
 
 /* C[z] = A[z] . W[z]^T with a fused epilogue. impl: 0 = default for dtype, 1 = SIMT, 2 = tcgen05 single-CTA kernels

@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("PI0_LIB") or os.path.join(_HERE, "libpi0b200.so")  # 
 
 SIGLIP_LAYERS = 27
 GEMMA_LAYERS = 18
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 c_f32p = C.c_void_p  # device pointers are opaque to ctypes
 c_ptr = C.c_void_p
@@ -69,6 +69,8 @@ class GemmDesc(C.Structure):
         ("rope_cos", c_ptr), ("rope_sin", c_ptr), ("pos_ids", c_ptr),
         ("kcache", c_ptr), ("n_q_heads", C.c_int32), ("kv_pitch", C.c_int64),
         ("dt", C.c_float), ("splits", C.c_int32),
+        ("rowsq_out", c_ptr), ("rowsq_ld", C.c_int32),
+        ("norm_gain", c_ptr), ("norm_rowsq", c_ptr), ("norm_slots", C.c_int32), ("norm_eps", C.c_float),
     ]
 
 

@@ -39,6 +39,9 @@ static int problem_from_desc(const pi0_gemm_desc* d, GemmProblem& g) {
   e.rope_cos = d->rope_cos; e.rope_sin = d->rope_sin; e.pos_ids = d->pos_ids;
   e.kcache = d->kcache; e.n_q_heads = d->n_q_heads; e.kv_pitch = d->kv_pitch;
   e.dt = d->dt;
+  e.rowsq_out = d->rowsq_out; e.rowsq_ld = d->rowsq_ld;
+  g.norm_gain = d->norm_gain; g.norm_rowsq = d->norm_rowsq; g.norm_slots = d->norm_slots;
+  g.norm_eps = d->norm_eps != 0.0f ? d->norm_eps : 1e-6f;
   return 0;
 }
 

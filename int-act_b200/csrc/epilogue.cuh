@@ -39,6 +39,10 @@ struct EpiParams {
   int64_t kv_pitch;       // rows per sample in kcache
   // EPI_EULER
   float dt;
+  // EPI_STORE, optional: sum of squares of the stored (rounded) values of every 32-column chunk -> rowsq_out[row * rowsq_ld +
+  // col0 / 32]; the next GEMM's fused RMSNorm sums the slots of a row in slot order (deterministic, no atomics)
+  float* rowsq_out;
+  int rowsq_ld;
 };
 
 __host__ inline EpiParams epi_default() {
@@ -49,6 +53,7 @@ __host__ inline EpiParams epi_default() {
   e.vt = nullptr; e.vt_col0 = 0x7fffffff; e.vt_hd = 1; e.vt_heads = 1; e.vt_rpb = 1; e.vt_toff = 0; e.vt_pitch = 0;
   e.rope_cos = nullptr; e.rope_sin = nullptr; e.pos_ids = nullptr; e.kcache = nullptr; e.n_q_heads = 0; e.kv_pitch = 0;
   e.dt = 0.0f;
+  e.rowsq_out = nullptr; e.rowsq_ld = 0;
   return e;
 }
 
@@ -173,6 +178,15 @@ __device__ __forceinline__ void epi_store_chunk(const EpiParams& ep, int row, in
         for (int j = 0; j < 8; ++j) v[g * 8 + j] += r[j];
       }
     }
+  }
+  if (ep.rowsq_out != nullptr) {
+    float q = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float r = Num<T>::rnd(v[j]);
+      if (j < ngroups * 8) q = fmaf(r, r, q);
+    }
+    ep.rowsq_out[(int64_t)row * ep.rowsq_ld + (col0 >> 5)] = q;
   }
   if (!direct_store) return;
   T* out = reinterpret_cast<T*>(ep.out) + zoff + epi_out_row(ep, row) * ep.ldc + col0;

@@ -201,11 +201,90 @@ __device__ __forceinline__ void drain_tile(const TcShape& sh, const EpiParams& e
   }
 }
 
-template <int BN, int EPI>
+// NormArgs: Gemma's RMSNorm fused into the A operand. The A tiles hold the RAW residual stream; the eight epilogue warps - idle
+// during the main loop when a CTA owns a single tile - rewrite every landed A tile in shared memory as
+// rnd((a * rstd[row]) * gain[k]) (the arithmetic of rmsnorm_warp_kernel) between the TMA's arrival and the MMA.
+struct NormArgs {
+  const float* gain;    // [K] fp32, 1 + w
+  const float* rowsq;   // [M][slots] per-chunk sums of squares of the rows of A (EpiParams.rowsq_out of the producing GEMM)
+  int slots;
+  float eps;
+};
+
+// executed by the 256 threads of warps 2..9 (t = threadIdx.x - 64) for k-blocks [kb0, kb1) of M-tile tm
+template <int BN>
+__device__ __forceinline__ void norm_a_operand(uint8_t* smem, uint64_t* full_bar, uint64_t* ready_bar, float* rstd_s,
+                                               const NormArgs& na, const TcShape& sh, int tm, int kb0, int kb1, int t) {
+  using Cfg = TcCfg<BN>;
+  const int lane = threadIdx.x & 31;
+  {
+    // rstd of the tile's rows: two threads per row, each sums half of the row's slots from independent 16-byte loads (a
+    // scalar loop over the slots is a chain of dependent L2 round trips: measured +18 us per launch), fixed order
+    const int r = t >> 1, hf = t & 1;
+    const int row = tm * kBM + r;
+    const int n4 = na.slots >> 3;          // float4 groups per half (slots % 8 == 0)
+    float q = 0.0f;
+    if (row < sh.M) {
+      const float4* rq = reinterpret_cast<const float4*>(na.rowsq + (int64_t)row * na.slots) + hf * n4;
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = i < n4 ? __ldcg(rq + i) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) q += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+      for (int i = 8; i < n4; ++i) { const float4 w = __ldcg(rq + i); q += (w.x + w.y) + (w.z + w.w); }
+    }
+    q += __shfl_xor_sync(0xffffffffu, q, 1);
+    if (hf == 0) rstd_s[r] = row < sh.M ? rsqrtf(q / (float)sh.K + na.eps) : 0.0f;
+  }
+  asm volatile("bar.sync 2, 256;" ::: "memory");
+  // piece i = t + 256 * qq of the [128 rows][8 pieces] tile: row (t >> 3) + 32 qq, physical piece t & 7. Under the 128-byte
+  // swizzle its logical k offset (ph ^ (row & 7)) * 8 is the SAME for all four pieces of a thread, so a thread needs eight
+  // gains per k-block: they are fetched one k-block ahead (a first touch of the gain vector costs an L2 round trip per
+  // k-block otherwise: measured +10 us on a 16-k-block GEMM).
+  const int ph = t & 7, r0 = t >> 3;
+  const int kofs = (ph ^ (r0 & 7)) << 3;
+  float4 g0 = __ldg(reinterpret_cast<const float4*>(na.gain + kb0 * kBK + kofs));
+  float4 g1 = __ldg(reinterpret_cast<const float4*>(na.gain + kb0 * kBK + kofs + 4));
+  int stage = 0;
+  uint32_t phase = 0;
+  for (int kb = kb0; kb < kb1; ++kb) {
+    const int kn = (kb + 1 < kb1 ? kb + 1 : kb) * kBK + kofs;
+    const float4 n0 = __ldg(reinterpret_cast<const float4*>(na.gain + kn));
+    const float4 n1 = __ldg(reinterpret_cast<const float4*>(na.gain + kn + 4));
+    mbar_wait(&full_bar[stage], phase);
+    uint8_t* sa = smem + stage * Cfg::kStageBytes;
+#pragma unroll
+    for (int qq = 0; qq < (kBM * 8) / 256; ++qq) {
+      const int r = r0 + 32 * qq;
+      uint4* pp = reinterpret_cast<uint4*>(sa + r * 128 + ph * 16);
+      const uint4 x = *pp;
+      const float rs = rstd_s[r];
+      const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x);
+      const float2 a0 = __bfloat1622float2(xh[0]), a1 = __bfloat1622float2(xh[1]);
+      const float2 a2 = __bfloat1622float2(xh[2]), a3 = __bfloat1622float2(xh[3]);
+      uint4 o;
+      o.x = bf16x2_bits((a0.y * rs) * g0.y, (a0.x * rs) * g0.x);
+      o.y = bf16x2_bits((a1.y * rs) * g0.w, (a1.x * rs) * g0.z);
+      o.z = bf16x2_bits((a2.y * rs) * g1.y, (a2.x * rs) * g1.x);
+      o.w = bf16x2_bits((a3.y * rs) * g1.w, (a3.x * rs) * g1.z);
+      *pp = o;
+    }
+    fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async-proxy reads
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&ready_bar[stage]);
+    g0 = n0;
+    g1 = n1;
+    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+  }
+}
+
+// NORM (fused RMSNorm of the A operand, norm_a_operand): only launched with at most ONE tile per CTA, so that the epilogue warps
+// are free during the tile's main loop.
+template <int BN, int EPI, bool NORM = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmC, const TcShape sh,
-               const EpiParams ep) {
+               const EpiParams ep, const NormArgs na) {
   using Cfg = TcCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -214,6 +293,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* ready_bar = tempty_bar + 3;                                  // NORM: A tile of the stage normalised
+  float* rstd_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 256);   // NORM: [128]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -234,6 +315,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(&tfull_bar[a], 1);
       mbar_init(&tempty_bar[a], 8);
     }
+    if constexpr (NORM)
+      for (int s = 0; s < Cfg::kStages; ++s) mbar_init(&ready_bar[s], 8);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
@@ -300,7 +383,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #ifdef PI0_TIMELINE
         long long m0 = clock64();
 #endif
-        mbar_wait(&full_bar[stage], phase);
+        mbar_wait(NORM ? &ready_bar[stage] : &full_bar[stage], phase);
 #ifdef PI0_TIMELINE
         long long m1 = clock64();
 #endif
@@ -358,6 +441,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int z0 = z % sh.nz0, z1 = z / sh.nz0;
       const int row = tm * kBM + quad * 32 + lane;
       const bool row_ok = row < sh.M;
+      if constexpr (NORM) norm_a_operand<BN>(smem, full_bar, ready_bar, rstd_s, na, sh, tm, 0, num_k, (int)threadIdx.x - 64);
 #ifdef PI0_TIMELINE
       if (threadIdx.x == 64 && idx == (int)blockIdx.x && num_k >= Cfg::kStages) {
         mbar_wait(&full_bar[Cfg::kStages - 1], 0);  // when does the LAST stage of the first ring pass land?
@@ -718,10 +802,11 @@ __device__ __forceinline__ void splitk_fetch(uint32_t stage_u32, int splits, int
   }
 }
 
-template <int BN, int EPI>
+// NORM: fused RMSNorm of the A operand (norm_a_operand above)
+template <int BN, int EPI, bool NORM = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcShape sh,
-                      const EpiParams ep) {
+                      const EpiParams ep, const NormArgs na) {
   using Cfg = TcCfg<BN>;
   static_assert((uint32_t)BN * kBM * 4 <= Cfg::kStages * Cfg::kStageBytes, "partial tile must fit the operand ring");
   extern __shared__ uint8_t smem_raw[];
@@ -730,6 +815,8 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + 4);
+  uint64_t* ready_bar = tfull_bar + 5;                                   // NORM: A tile of the stage normalised
+  float* rstd_s = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 256);   // NORM: [128] (launch adds 1 KiB)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -746,6 +833,8 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(&tfull_bar[0], 1);
+    if constexpr (NORM)
+      for (int s = 0; s < Cfg::kStages; ++s) mbar_init(&ready_bar[s], 8);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<(BN < 32 ? 32 : BN)>(tmem_slot);
@@ -780,7 +869,7 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = kb0; kb < kb1; ++kb) {
-      mbar_wait(&full_bar[stage], phase);
+      mbar_wait(NORM ? &ready_bar[stage] : &full_bar[stage], phase);
       tc_fence_after();
       if (elect_one()) {
         const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -796,6 +885,8 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
     }
   } else {
+    if constexpr (NORM)
+      norm_a_operand<BN>(smem, full_bar, ready_bar, rstd_s, na, sh, tm, kb0, kb1, (int)threadIdx.x - 64);
     // spill this CTA's partial accumulator: TMEM -> smem [col][row] (the operand ring is drained once tfull fires)
     const int quad = warp & 3;
     const int half = (warp - 2) >> 2;
@@ -1134,7 +1225,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   }
   if (sh.splits > 1) {
     PI0_CHECK_CUDA(launch_pdl(gemm_tc_splitk_kernel<BN, EPI>, dim3((unsigned)(sh.total_tiles * sh.splits)),
-                              dim3(kTcThreads), Cfg::kSmemBytes, stream, sh.splits, tmA, tmB, sh, g.epi));
+                              dim3(kTcThreads), Cfg::kSmemBytes, stream, sh.splits, tmA, tmB, sh, g.epi, NormArgs{nullptr, nullptr, 0, 0.0f}));
   } else {
     int grid = sh.total_tiles < num_sms ? sh.total_tiles : num_sms;
     CUtensorMap tmC = tmA;
@@ -1142,7 +1233,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
     if (have_c < 0) return have_c;
     sh.tma_store = have_c;
     PI0_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, EPI>, dim3((unsigned)grid), dim3(kTcThreads), Cfg::kSmemBytesStaged,
-                              stream, 1, tmA, tmB, tmC, sh, g.epi));
+                              stream, 1, tmA, tmB, tmC, sh, g.epi, NormArgs{nullptr, nullptr, 0, 0.0f}));
   }
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
@@ -1318,6 +1409,64 @@ void gemm_tc_pick(int M, int N, int K, int nz, int num_sms, bool fixed_bn, int* 
   *splits_out = best_s;
 }
 
+// ---- Gemma RMSNorm fused into the A operand (GemmProblem.norm_gain): the one-tile-per-CTA cluster kernel with NORM = true,
+// bn = 256, the q|k|v (RoPE) and gate/up (GeGLU) epilogues; splits = 1 is a cluster of one ----
+template <int EPI>
+static int launch_norm(const GemmProblem& g, int splits, int num_sms, cudaStream_t stream) {
+  constexpr int BN = 256;
+  using Cfg = TcCfg<BN>;
+  constexpr uint32_t kSmem = Cfg::kSmemBytes + 1024;   // + the per-row rstd table
+  static PerDeviceOnce attr_once;
+  if (attr_once.need()) {
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_splitk_kernel<BN, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)kSmem));
+    attr_once.mark();
+  }
+  PI0_REQUIRE(g.K % kBK == 0 && g.nz0 * g.nz1 == 1, "gemm_tc (fused norm): K=%d must be a multiple of 64, no batching", g.K);
+  PI0_REQUIRE(g.norm_rowsq != nullptr && g.norm_slots >= 8 && g.norm_slots % 8 == 0,
+              "gemm_tc (fused norm): row statistics missing or slots=%d not a multiple of 8", g.norm_slots);
+  CUtensorMap tmA, tmB;
+  const int a_rows = g.M < kBM ? ((g.M + 7) / 8) * 8 : kBM;
+  PI0_TRY(make_map(&tmA, g.A, g.K, g.M, 1, 1, g.lda, 0, 0, a_rows));
+  PI0_TRY(make_map(&tmB, g.W, g.K, g.N, 1, 1, g.ldw, 0, 0, BN));
+  TcShape sh;
+  sh.M = g.M; sh.N = g.N; sh.K = g.K; sh.nz0 = 1; sh.nz1 = 1;
+  sh.tiles_m = (g.M + kBM - 1) / kBM;
+  sh.tiles_n = (g.N + BN - 1) / BN;
+  sh.total_tiles = sh.tiles_m * sh.tiles_n;
+  set_super(sh, kBM);
+  const int num_k = g.K / kBK;
+  const int per = (num_k + splits - 1) / splits;
+  sh.splits = (num_k + per - 1) / per;
+  sh.kb_per_split = per;
+  sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
+  sh.tma_store = 0;
+  const NormArgs na{g.norm_gain, g.norm_rowsq, g.norm_slots, g.norm_eps};
+  if (sh.splits == 1 && sh.total_tiles <= num_sms) {
+    // one tile per CTA without a k split: the persistent kernel, which keeps its TMA-store epilogue
+    static PerDeviceOnce attr2;
+    if (attr2.need()) {
+      PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)Cfg::kSmemBytesStaged));
+      attr2.mark();
+    }
+    CUtensorMap tmC = tmA;
+    const int have_c = make_out_map(&tmC, g);
+    if (have_c < 0) return have_c;
+    sh.tma_store = have_c;
+    PI0_CHECK_CUDA(launch_pdl(gemm_tc_kernel<BN, EPI, true>, dim3((unsigned)sh.total_tiles), dim3(kTcThreads),
+                              Cfg::kSmemBytesStaged, stream, 1, tmA, tmB, tmC, sh, g.epi, na));
+    PI0_CHECK_CUDA(cudaGetLastError());
+    ++g_launch_count;
+    return 0;
+  }
+  PI0_CHECK_CUDA(launch_pdl(gemm_tc_splitk_kernel<BN, EPI, true>, dim3((unsigned)(sh.total_tiles * sh.splits)),
+                            dim3(kTcThreads), kSmem, stream, sh.splits, tmA, tmB, sh, g.epi, na));
+  PI0_CHECK_CUDA(cudaGetLastError());
+  ++g_launch_count;
+  return 0;
+}
+
 int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   PI0_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "gemm_tc: empty problem M=%d N=%d K=%d", g.M, g.N, g.K);
   // a ragged N is fine for EPI_STORE when nothing is read per column and the row pitch covers the 8-wide store
@@ -1333,6 +1482,12 @@ int gemm_tc_launch(const GemmProblem& g, int num_sms, cudaStream_t stream) {
     if (sp == 0) sp = auto_s;
   }
   PI0_REQUIRE(sp >= 1 && sp <= 8, "gemm_tc: splits=%d outside [1,8]", sp);
+  if (g.norm_gain != nullptr) {
+    PI0_REQUIRE(bn == 256 && (g.epi_mode == EPI_ROPE || g.epi_mode == EPI_GEGLU),
+                "gemm_tc (fused norm): only the bn = 256 RoPE / GeGLU GEMMs take a fused RMSNorm");
+    if (g.epi_mode == EPI_ROPE) return launch_norm<EPI_ROPE>(g, sp, num_sms, stream);
+    return launch_norm<EPI_GEGLU>(g, sp, num_sms, stream);
+  }
   if (use_pair(g, bn, num_sms)) {
     switch (g.epi_mode) {
       case EPI_STORE:

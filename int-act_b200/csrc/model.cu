@@ -86,6 +86,10 @@ struct pi0_ctx {
   void* x3_w;
   void* x3_p;  // fp32 partial sums of the split-K form (skinny problems)
   size_t x3_a_bytes, x3_w_bytes, x3_p_bytes;
+  float* rowsq_x;  // fused RMSNorm of the rollout-batch denoise path: per-chunk sums of squares of the residual stream rows
+  float* rowsq_y;  // ... and of the post-attention stream (written by the o_proj / down epilogues)
+  bool norm_fuse;  // PI0_NORM_FUSE=0 disables
+  int norm_fuse_max_rows;  // largest M = B x S that takes the fused norms (PI0_NORM_FUSE_MAX_ROWS, default 64)
   X3WeightCache x3_cache;  // split copies of the GEMM weights (PI0_FP32_WCACHE=0 disables)
   bool attn_split;  // two-launch denoise attention for B >= 4 (PI0_ATTN_SPLIT=0 disables)
   bool prefill_fused;  // fused tcgen05 prefix attention (PI0_PREFILL_FUSED=0 disables)
@@ -222,6 +226,8 @@ void carve(Carver& cv, pi0_ctx* c, const pi0_model_cfg& cfg) {
   x.loop_units = (int16_t*)cv.take("loop.units", loop_units_bytes());
   x.loop_ll = (uint4*)cv.take("loop.ll", loop_ll_bytes());
   x.loop_epoch = (unsigned*)cv.take("loop.epoch", 64);
+  x.rowsq_x = (float*)cv.take("suffix.rowsq_x", Me * (kExpHidden / 32) * 4);
+  x.rowsq_y = (float*)cv.take("suffix.rowsq_y", Me * (kExpHidden / 32) * 4);
   x.x3_a = x.x3_w = x.x3_p = nullptr;
   x.x3_a_bytes = x.x3_w_bytes = x.x3_p_bytes = 0;
   if (cfg.dtype == 1 && fp32_x3_enabled()) {
@@ -341,7 +347,10 @@ struct LayerIO {
   void* x_out;       // after MLP           [M, hidden]
 };
 
-int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bool kv_only, cudaStream_t s) {
+// x_stats: the rows of io.x_in come with per-chunk sums of squares in c->rowsq_x (left by the previous layer's down projection),
+// so the input RMSNorm can be fused into the q|k|v GEMM
+int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bool kv_only, cudaStream_t s,
+                bool x_stats = false, bool* out_stats = nullptr) {
   const int es = c->es;
   const int T = suffix ? c->S : c->P;            // tokens per sample in this pass
   const int M = B * T;
@@ -392,12 +401,23 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     return 0;
   }
 
+  // Denoise step of a rollout batch on the tcgen05 per-op path: both RMSNorms of the layer are fused into the A operand of the
+  // GEMM that consumes them (norm_a_operand in gemm_tc.cu); the row statistics come from the epilogues of the o_proj / down
+  // projections that produce the streams. Saves two launches per layer-step (360 per denoise loop) but puts ~0.3 us per
+  // k-block on the critical path of two latency-bound GEMMs: measured -2.6 % per infer at batch 8, -1 % at 16, 0 at 24 / 32,
+  // +2 % at batch 64 (the stand-alone norm kernels hide behind PDL there). Hence the row limit (default 64 = batch 12).
+  const bool fuse = suffix && c->norm_fuse && M <= c->norm_fuse_max_rows && c->cfg.dtype == 0 && c->cfg.gemm_impl == 0;
+  const int slots = hidden / 32;
+  if (out_stats) *out_stats = fuse;
+
   // input RMSNorm
-  PI0_TRY(run_rmsnorm(c, L[0], io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
+  if (!(fuse && x_stats)) PI0_TRY(run_rmsnorm(c, L[0], io.x_in, h, w.g1, M, hidden, 0, 0, 0, s));
 
   // fused QKV + RoPE; K and V^T land in the cache (mllm.py:216-221 + fill_kv_cache)
   {
-    GemmProblem g = gemm_problem(h, hidden, w.wqkv, hidden, M, (kHeads + 2) * kHd, hidden);
+    GemmProblem g = fuse && x_stats ? gemm_problem(io.x_in, hidden, w.wqkv, hidden, M, (kHeads + 2) * kHd, hidden)
+                                    : gemm_problem(h, hidden, w.wqkv, hidden, M, (kHeads + 2) * kHd, hidden);
+    if (fuse && x_stats) { g.norm_gain = w.g1; g.norm_rowsq = c->rowsq_x; g.norm_slots = slots; g.norm_eps = kEps; }
     g.epi_mode = EPI_ROPE; g.bn = 256;
     g.epi.out = q; g.epi.ldc = kHidden;
     g.epi.rope_cos = c->w.rope_cos; g.epi.rope_sin = c->w.rope_sin;
@@ -475,12 +495,15 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     GemmProblem g = gemm_problem(att, kHidden, w.wo, kHidden, M, hidden, kHidden);
     g.bn = 0;
     g.epi.out = io.y; g.epi.ldc = hidden; g.epi.res = io.x_in; g.epi.ldr = hidden;
+    if (fuse) { g.epi.rowsq_out = c->rowsq_y; g.epi.rowsq_ld = slots; }
     PI0_TRY(run_gemm(c, L[5], g, s));
   }
-  PI0_TRY(run_rmsnorm(c, L[6], io.y, h, w.g2, M, hidden, 0, 0, 0, s));
+  if (!fuse) PI0_TRY(run_rmsnorm(c, L[6], io.y, h, w.g2, M, hidden, 0, 0, 0, s));
   // GeGLU: gate/up interleaved per 256-row tile at pack time
   {
-    GemmProblem g = gemm_problem(h, hidden, w.wgu, hidden, M, 2 * inter, hidden);
+    GemmProblem g = fuse ? gemm_problem(io.y, hidden, w.wgu, hidden, M, 2 * inter, hidden)
+                         : gemm_problem(h, hidden, w.wgu, hidden, M, 2 * inter, hidden);
+    if (fuse) { g.norm_gain = w.g2; g.norm_rowsq = c->rowsq_y; g.norm_slots = slots; g.norm_eps = kEps; }
     g.epi_mode = EPI_GEGLU; g.bn = 256;
     g.epi.out = act; g.epi.ldc = inter;
     PI0_TRY(run_gemm(c, L[7], g, s));
@@ -489,6 +512,7 @@ int gemma_layer(pi0_ctx* c, int B, int layer, bool suffix, const LayerIO& io, bo
     GemmProblem g = gemm_problem(act, inter, w.wdown, inter, M, hidden, inter);
     g.bn = 0;
     g.epi.out = io.x_out; g.epi.ldc = hidden; g.epi.res = io.y; g.epi.ldr = hidden;
+    if (fuse) { g.epi.rowsq_out = c->rowsq_x; g.epi.rowsq_ld = slots; }
     PI0_TRY(run_gemm(c, L[8], g, s));
   }
   return 0;
@@ -550,6 +574,9 @@ int pi0_ctx_create(const pi0_model_cfg* cfg, const pi0_weights* w, void* workspa
     c->attn_split = !(e && strcmp(e, "0") == 0);
     const char* f = getenv("PI0_SIGLIP_FUSED");
     c->siglip_fused = !(f && strcmp(f, "0") == 0);
+    const char* nf = getenv("PI0_NORM_FUSE");
+    c->norm_fuse = !(nf && strcmp(nf, "0") == 0);
+    c->norm_fuse_max_rows = getenv("PI0_NORM_FUSE_MAX_ROWS") ? atoi(getenv("PI0_NORM_FUSE_MAX_ROWS")) : 64;
     const char* pf = getenv("PI0_PREFILL_FUSED");
     c->prefill_fused = !(pf && strcmp(pf, "0") == 0);
     const char* pm = getenv("PI0_PREFILL_FUSED_MIN_TILES");
@@ -1010,9 +1037,12 @@ int pi0_denoise_loop(pi0_ctx* c, int B, const float* state, float* x_t, void* st
       mp.kp = (c->P + S + 31) / 32 * 32; mp.sc = (bf16*)c->mega_sc;
       PI0_TRY(mega_denoise_layers(mp, c->mega_ctas, s));
     } else {
+      bool stats = false;   // layer 0 reads the suffix embeddings, which come without row statistics
       for (int l = 0; l < c->cfg.n_gemma_layers; ++l) {
         LayerIO io{l == 0 ? c->suf : c->xe, c->ye, c->xe};
-        PI0_TRY(gemma_layer(c, B, l, true, io, false, s));
+        bool produced = false;
+        PI0_TRY(gemma_layer(c, B, l, true, io, false, s, stats, &produced));
+        stats = produced;
       }
     }
     // final norm on the last H rows of every sample, action_out_proj and the Euler update x_t += dt * v_t

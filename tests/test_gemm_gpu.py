@@ -268,3 +268,45 @@ def test_gemm_tc_throughput_report(cuda):
         print(f"\n[tc gemm] M={M} N={N} K={K} bn={bn}: {ms:.3f} ms  {2.0 * M * N * K / ms / 1e9:.1f} TFLOP/s")
     ref = _ref_linear(A[:256], W[:256])
     assert (out[:256, :256].float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item() + 1e-3
+
+
+# ---- GemmaRMSNorm fused into the A operand (rollout-batch denoise path) -------------------------------------------------
+@pytest.mark.parametrize("M,K,inter,splits", [(320, 1024, 1024, 1), (40, 1024, 512, 2), (130, 2048, 256, 4)])
+def test_gemm_fused_rmsnorm_matches_norm_then_gemm(cuda, M, K, inter, splits):
+    """Producer: a residual GEMM whose epilogue leaves per-chunk sums of squares of its output rows (rowsq_out). Consumer: the
+    gate/up GeGLU GEMM with the RAW stream as A and the RMSNorm applied in shared memory (norm_gain / norm_rowsq), against
+    pi0_rmsnorm followed by the plain GEMM - same arithmetic, so the two agree up to the summation order of the row statistic."""
+    Kp = 512
+    A0 = _rand((M, Kp), cuda, seed=31)
+    Wp = _rand((K, Kp), cuda, 0.04, seed=32)
+    res = _rand((M, K), cuda, seed=33)
+    y = torch.zeros((M, K), dtype=torch.bfloat16, device=cuda)
+    rowsq = torch.full((M, K // 32), float("nan"), dtype=torch.float32, device=cuda)
+    pb.gemm(A0, Wp, y, res=res, bn=0, splits=0, rowsq_out=rowsq, rowsq_ld=K // 32)
+    torch.cuda.synchronize()
+    ref_sq = (y.float() ** 2).view(M, K // 32, 32).sum(-1)
+    assert torch.isfinite(rowsq).all()
+    assert (rowsq - ref_sq).abs().max().item() <= 1e-3 * ref_sq.abs().max().item()
+
+    gain = (1.0 + 0.1 * torch.randn(K, generator=torch.Generator().manual_seed(34))).to(cuda)
+    Wg = _rand((inter, K), cuda, 0.03, seed=35)
+    Wu = _rand((inter, K), cuda, 0.03, seed=36)
+    Wgu = torch.stack([Wg.view(-1, 128, K), Wu.view(-1, 128, K)], dim=1).reshape(2 * inter, K).contiguous()
+    fused = torch.zeros((M, inter), dtype=torch.bfloat16, device=cuda)
+    pb.gemm(y, Wgu, fused, epi_mode=pb.EPI_GEGLU, bn=256, splits=splits, norm_gain=gain, norm_rowsq=rowsq,
+            norm_slots=K // 32, norm_eps=1e-6)
+    h = torch.zeros_like(y)
+    pb.check(pb.lib().pi0_rmsnorm(pb.ptr(y), pb.ptr(h), pb.ptr(gain), M, K, 0, pb.current_stream()), "pi0_rmsnorm")
+    plain = torch.zeros_like(fused)
+    pb.gemm(h, Wgu, plain, epi_mode=pb.EPI_GEGLU, bn=256, splits=splits)
+    torch.cuda.synchronize()
+    assert torch.isfinite(fused.float()).all()
+    dif = (fused.float() - plain.float()).abs().max().item()
+    scale = max(1.0, plain.float().abs().max().item())
+    assert dif <= 2 ** -7 * scale, dif          # at most a flipped bf16 rounding here and there
+    assert (fused != plain).float().mean().item() < 0.02
+    hh = (y.float() * torch.rsqrt((y.float() ** 2).mean(-1, keepdim=True) + 1e-6) * gain).bfloat16().float()
+    g = (hh @ Wg.float().t()).bfloat16().float()
+    u = (hh @ Wu.float().t()).bfloat16().float()
+    ref = (torch.nn.functional.gelu(g, approximate="tanh").bfloat16().float() * u).bfloat16().float()
+    assert (fused.float() - ref).abs().max().item() <= 3e-2 * max(1.0, ref.abs().max().item())

@@ -117,6 +117,27 @@ def test_batch_above_96_takes_the_blocked_attention_kernel_in_the_denoise_step(c
     assert err <= 1e-2, err
 
 
+def test_fused_rmsnorm_of_the_rollout_denoise_path_against_the_separate_norm_kernels(cuda, monkeypatch):
+    """Batch 16 (per-op tcgen05 denoise path): RMSNorms fused into the q|k|v / gate-up GEMMs (default up to 64 suffix rows; the
+    limit is lifted here) against PI0_NORM_FUSE=0 and the oracle; the fused path launches 2 x layers - 1 fewer kernels per
+    Euler step."""
+    dims = Dims(n_siglip_layers=1, n_gemma_layers=3, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=6)
+    B = 16
+    inp = synthetic_inputs(B, vocab=dims.vocab, n_valid_text=[72, 9, 33, 2, 50, 17, 64, 1])
+    monkeypatch.setenv("PI0_NORM_FUSE_MAX_ROWS", "512")
+    eng, out = _engine_out(cuda, sd, "bf16", B, inp)
+    monkeypatch.setenv("PI0_NORM_FUSE", "0")
+    eng0, out0 = _engine_out(cuda, sd, "bf16", B, inp)
+    ref = oracle_for(sd, dims, 1, 72, 4, "bf16").sample_actions(*inp)
+    err, err0, dif = (out - ref).abs().max().item(), (out0 - ref).abs().max().item(), (out - out0).abs().max().item()
+    saved = eng0.launches_per_infer[B] - eng.launches_per_infer[B]
+    print(f"\n[fused rmsnorm B={B}] vs oracle {err:.3e} (separate norms {err0:.3e}); fused vs separate {dif:.3e}; "
+          f"{saved} launches fewer per infer")
+    assert err <= 1e-2 and dif <= 1e-2
+    assert saved == 10 * (2 * dims.n_gemma_layers - 1)
+
+
 def test_state_row_and_vacuity_guards(cuda):
     """Zeroing the state moves the action by only ~1e-2 (the tolerance), so a broken state_proj path could hide behind the
     action check: the state row of the suffix embedding is compared directly."""
