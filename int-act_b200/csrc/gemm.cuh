@@ -17,6 +17,8 @@ struct GemmProblem {
   int bn;                   // N tile of the tcgen05 kernel (32/64/128/256; 0 = auto); EPI_ROPE requires 256
   int splits;               // split-K factor = cluster size (1..8; 0 = auto)
   int pair;                 // CTA-pair (cta_group::2) kernel: 0 = auto, 1 = force, -1 = never
+  int w_const;              // 1: W is a constant parameter matrix (never written by a preceding kernel): its first tiles may be
+                            // fetched before the programmatic-dependency wait
   // Gemma RMSNorm fused into the A operand (tcgen05 path, EPI_ROPE / EPI_GEGLU, bn 256): A holds the RAW residual stream, the
   // kernel forms rnd((a * rstd[row]) * norm_gain[k]) in shared memory before the MMA; rstd[row] = rsqrt(sum of the row's
   // norm_slots entries of norm_rowsq / K + eps), the per-chunk sums of squares left by the producing GEMM (EpiParams.rowsq_out)
@@ -33,6 +35,7 @@ inline GemmProblem gemm_problem(const void* A, int64_t lda, const void* W, int64
   g.W = W; g.ldw = ldw; g.w_z0 = 0; g.w_z1 = 0;
   g.M = M; g.N = N; g.K = K; g.nz0 = 1; g.nz1 = 1;
   g.epi_mode = EPI_STORE; g.bn = 256; g.splits = 0; g.pair = 0;
+  g.w_const = 0;
   g.norm_gain = nullptr; g.norm_rowsq = nullptr; g.norm_slots = 0; g.norm_eps = 1e-6f;
   g.epi = epi_default();
   return g;

@@ -56,6 +56,8 @@ struct TcShape {
   uint32_t stage_tx; // bytes one pipeline stage receives: A box (rows clipped to M for a single short M tile) + W box
   int tma_store;     // 1: EPI_STORE / EPI_GEGLU output goes through shared memory and tensor-map stores (tmC valid)
   int super_m, super_n;  // second-level tile blocking for wide problems (tiles), see tile_coords
+  int w_prefetch;    // 1: W is a constant weight matrix - the TMA warp requests the W boxes of the first ring stages BEFORE the
+                     // programmatic-dependency wait, so the weight fetch (cold HBM) overlaps the previous kernel's tail
 };
 
 // Tile order of the persistent kernels. Small problems: groups of kGroupM M-tiles, M fastest inside a group, so that the
@@ -325,7 +327,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int num_k = (sh.K + kBK - 1) / kBK;
-  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory is touched only below
+  // weights do not depend on the previous kernel: the W boxes of the CTA's first tile, first ring pass, are requested now
+  const int pre = sh.w_prefetch && (int)blockIdx.x < sh.total_tiles ? min(num_k, Cfg::kStages) : 0;
+  if (pre > 0 && warp == 0 && elect_one()) {
+    int z, tm, tn;
+    tile_coords(sh, blockIdx.x, z, tm, tn);
+    for (int kb = 0; kb < pre; ++kb) {
+      mbar_arrive_expect_tx(&full_bar[kb], sh.stage_tx);
+      tma_load_4d(smem + kb * Cfg::kStageBytes + Cfg::kABytes, &tmB, &full_bar[kb], kb * kBK, tn * BN, z % sh.nz0, z / sh.nz0);
+    }
+  }
+  pdl_wait();  // everything above overlapped the previous kernel's tail; activations are touched only below
   if (threadIdx.x == 0) PI0_STAMP(1);
 
   if (warp == 0) {
@@ -347,7 +359,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #endif
           uint8_t* sa = smem + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
+          const bool prefetched = idx == (int)blockIdx.x && kb < pre;   // barrier armed and W requested before the wait
+          if (!prefetched) mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
 #ifdef PI0_TIMELINE
           long long c2 = clock64();
 #endif
@@ -355,7 +368,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #ifdef PI0_TIMELINE
           long long c3 = clock64();
 #endif
-          tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+          if (!prefetched) tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
 #ifdef PI0_TIMELINE
           long long c4 = clock64();
           if (blockIdx.x == 0 && idx == 0 && kb == 2) {
@@ -845,10 +858,18 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int num_k = (sh.K + kBK - 1) / kBK;
   const int kb0 = rank * sh.kb_per_split;
   const int kb1 = min(num_k, kb0 + sh.kb_per_split);
-  pdl_wait();
   int z, tm, tn;
   tile_coords(sh, tile, z, tm, tn);
   const int z0 = z % sh.nz0, z1 = z / sh.nz0;
+  // weights do not depend on the previous kernel: the W boxes of the first ring pass are requested before the wait
+  const int pre = sh.w_prefetch ? min(kb1 - kb0, Cfg::kStages) : 0;
+  if (pre > 0 && warp == 0 && elect_one()) {
+    for (int i = 0; i < pre; ++i) {
+      mbar_arrive_expect_tx(&full_bar[i], sh.stage_tx);
+      tma_load_4d(smem + i * Cfg::kStageBytes + Cfg::kABytes, &tmB, &full_bar[i], (kb0 + i) * kBK, tn * BN, z0, z1);
+    }
+  }
+  pdl_wait();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -858,9 +879,10 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
-        mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
+        const bool prefetched = kb - kb0 < pre;
+        if (!prefetched) mbar_arrive_expect_tx(&full_bar[stage], sh.stage_tx);
         tma_load_4d(sa, &tmA, &full_bar[stage], kb * kBK, tm * kBM, z0, z1);
-        tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
+        if (!prefetched) tma_load_4d(sb, &tmB, &full_bar[stage], kb * kBK, tn * BN, z0, z1);
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
       }
     }
@@ -1216,6 +1238,7 @@ static int launch_cfg(const GemmProblem& g, int num_sms, int splits, cudaStream_
   sh.kb_per_split = num_k;
   sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
   sh.tma_store = 0;
+  sh.w_prefetch = g.w_const ? 1 : 0;
   if (splits > 1) {
     // every rank of the cluster must own at least one k-block
     int per = (num_k + splits - 1) / splits;
@@ -1288,6 +1311,7 @@ static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   sh.splits = 1;
   sh.kb_per_split = (g.K + kBK - 1) / kBK;
   sh.stage_tx = 2 * Cfg::kStageBytes;
+  sh.w_prefetch = 0;
   CUtensorMap tmC = tmA;
   const int have_c = make_out_map(&tmC, g);
   if (have_c < 0) return have_c;
@@ -1441,6 +1465,7 @@ static int launch_norm(const GemmProblem& g, int splits, int num_sms, cudaStream
   sh.kb_per_split = per;
   sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
   sh.tma_store = 0;
+  sh.w_prefetch = g.w_const ? 1 : 0;
   const NormArgs na{g.norm_gain, g.norm_rowsq, g.norm_slots, g.norm_eps};
   if (sh.splits == 1 && sh.total_tiles <= num_sms) {
     // one tile per CTA without a k split: the persistent kernel, which keeps its TMA-store epilogue
@@ -1555,6 +1580,7 @@ static int launch_f32out(const GemmProblem& g, int num_sms, void* partial, size_
   sh.kb_per_split = num_k;
   sh.stage_tx = (uint32_t)(a_rows * kBK * 2) + Cfg::kBBytes;
   sh.tma_store = 0;
+  sh.w_prefetch = 0;
   // split-K over CTAs when the tiles cover less than half of the SMs (denoise steps, batch-1 prefill): every CTA takes a
   // k-slice of >= 4 k-blocks and leaves its fp32 partial in the workspace; x3_reduce_kernel finishes
   const int ldp = (g.N + 31) / 32 * 32;

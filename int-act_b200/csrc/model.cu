@@ -311,6 +311,16 @@ int run_gemm(pi0_ctx* c, const char* label, const GemmProblem& g, cudaStream_t s
                                   &c->x3_cache, is_weight);
     if (rc != 1) return rc;   // 1: not eligible (ragged N with a bias, operand larger than the scratch) -> SIMT kernel
   }
+  static const bool w_pre = !(getenv("PI0_W_PREFETCH") && getenv("PI0_W_PREFETCH")[0] == '0');
+  if (w_pre && c->cfg.dtype == 0) {
+    // W outside the workspace = a weight (activations used as W - K cache, V^T - live inside): eligible for the early fetch
+    const uint8_t* wp = (const uint8_t*)g.W;
+    if (wp < c->base || wp >= c->base + c->ws_bytes) {
+      GemmProblem gw = g;
+      gw.w_const = 1;
+      return gemm_launch(gw, c->cfg.dtype, c->cfg.gemm_impl, sms, s);
+    }
+  }
   return gemm_launch(g, c->cfg.dtype, c->cfg.gemm_impl, sms, s);
 }
 
