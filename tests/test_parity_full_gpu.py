@@ -182,6 +182,27 @@ def test_mean_std_normalisation_through_the_policy(cuda):
     assert (out - ref).abs().max().item() <= 1e-2 * float(stats["action"]["std"].max()) + 1e-6
 
 
+def test_fp32_regime_through_the_policy(cuda):
+    """`--use_bf16 False` (the reference's shipped eval flag): PI0Policy.to(torch.float32) -> fp32 weights and activations, GEMMs
+    as split-bf16 products on the tensor cores (gemm_x3.cu) and the one-pass fp32 kernel for the denoise steps; <= 1e-4 against
+    the fp32 oracle at batch 1 and at a batch that leaves the skinny kernel (M = 70 suffix rows)."""
+    dims = Dims(n_siglip_layers=2, n_gemma_layers=3, vocab=1024)
+    sd = random_state_dict(dims, device=cuda, seed=8)
+    cfg = bridge_config()
+    for B, n_valid in [(1, [33]), (14, [72, 9, 33, 2, 50, 17, 64])]:
+        inp = synthetic_inputs(B, vocab=dims.vocab, n_valid_text=n_valid)
+        batch = {"observation.images.top": inp[0][0], "observation.state": inp[4], "lang_tokens": inp[2], "lang_masks": inp[3]}
+        pol = PI0Policy(cfg, None, state_dict=sd, device=cuda, max_batch=B)
+        pol.to(torch.float32)
+        out = pol.infer_action({k: (v.to(cuda) if torch.is_tensor(v) else v) for k, v in batch.items()},
+                               noise=inp[5].to(cuda)).cpu()
+        assert pol._engine.path_report(B)["gemm"] == "tcgen05_split_bf16x3_fp32"
+        ref = oracle_for(sd, dims, 1, cfg.tokenizer_max_length, cfg.n_action_steps, "fp32").sample_actions(*inp)
+        err = (out - ref[:, :, : out.shape[-1]]).abs().max().item()
+        print(f"\n[fp32 regime through the policy, B={B}] max-abs action error vs the fp32 oracle: {err:.3e}")
+        assert err <= 1e-4, err
+
+
 def test_masked_empty_camera_and_three_cameras(cuda):
     dims = Dims(n_siglip_layers=1, n_gemma_layers=2, vocab=1024)
     sd = random_state_dict(dims, device=cuda, seed=2)
