@@ -992,22 +992,27 @@ gemm_tc_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 // ready" arrivals to both CTAs, both producers signal their TMA bytes on the LEADER's full barrier, and both CTAs'
 // epilogue warps hand the accumulator buffer back on the leader's barrier.
 // ---------------------------------------------------------------------------------------------
-template <int BN>
+// EW = epilogue warps per TMEM lane quadrant (2 or 3). Short-K tiles (SigLIP, K = 1152: main loop 5.3 us per tile) are bound by
+// the 8 epilogue warps (6.1 us for a bias + GELU tile): with 12 warps a warp drains 3 instead of 4 of the tile's 8 column
+// chunks. The four extra staging buffers cost one ring stage.
+template <int BN, int EW = 2>
 struct Tc2Cfg {
   static constexpr uint32_t kABytes = kBM * kBK * 2;
   static constexpr uint32_t kBBytes = (BN / 2) * kBK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN == 256) ? 6 : 8;
+  static constexpr int kStages = (BN == 256) ? (EW == 2 ? 6 : 5) : 8;
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 1024 + kStoreStageBytes;
+  static constexpr int kThreads = 64 + 128 * EW;
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 1024 + 1024 + 4 * EW * 2 * kStoreBufBytes;
+  static_assert(kSmemBytes <= 232448, "shared memory budget of one SM");
 };
 
-template <int BN, int EPI>
-__global__ void __launch_bounds__(kTcThreads, 1)
+template <int BN, int EPI, int EW = 2>
+__global__ void __launch_bounds__(64 + 128 * EW, 1)
 gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const TcShape sh,
                     const EpiParams ep) {
-  using Cfg = Tc2Cfg<BN>;
+  using Cfg = Tc2Cfg<BN, EW>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -1033,7 +1038,7 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull_bar[a], 1);
-      mbar_init(&tempty_bar[a], 16);  // 8 epilogue warps of each CTA; only the leader's copy is waited on
+      mbar_init(&tempty_bar[a], 8 * EW);  // 4 EW epilogue warps of each CTA; only the leader's copy is waited on
     }
     fence_barrier_init();
   }
@@ -1120,7 +1125,7 @@ gemm_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tc_fence_after();
       if (threadIdx.x == 64) PAIR_STAMP(rank, (idx - pair) / n_pairs, 2);
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * BN;
-      drain_tile<BN, EPI>(sh, ep, taddr, row, row_ok, tn, z0, z1, half, &tmC, stage2, sbuf);
+      drain_tile<BN, EPI, EW>(sh, ep, taddr, row, row_ok, tn, z0, z1, half, &tmC, stage2, sbuf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
@@ -1290,12 +1295,12 @@ static int max_active_pairs(int num_sms) {
   return n;
 }
 
-template <int BN, int EPI>
-static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
-  using Cfg = Tc2Cfg<BN>;
+template <int BN, int EPI, int EW>
+static int launch_pair_ew(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  using Cfg = Tc2Cfg<BN, EW>;
   static PerDeviceOnce attr_once;
   if (attr_once.need()) {
-    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_pair_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PI0_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_pair_kernel<BN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)Cfg::kSmemBytes));
     attr_once.mark();
   }
@@ -1316,13 +1321,24 @@ static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
   const int have_c = make_out_map(&tmC, g);
   if (have_c < 0) return have_c;
   sh.tma_store = have_c;
-  const int cap = max_active_pairs<BN, EPI>(num_sms);
+  const int cap = max_active_pairs<BN, EPI>(num_sms);   // the EW = 2 kernel's figure: smem-bound (1 CTA per SM) for both
   const int pairs = sh.total_tiles < cap ? sh.total_tiles : cap;
-  PI0_CHECK_CUDA(launch_pdl(gemm_tc_pair_kernel<BN, EPI>, dim3((unsigned)(2 * pairs)), dim3(kTcThreads),
+  PI0_CHECK_CUDA(launch_pdl(gemm_tc_pair_kernel<BN, EPI, EW>, dim3((unsigned)(2 * pairs)), dim3(Cfg::kThreads),
                             Cfg::kSmemBytes, stream, 2, tmA, tmB, tmC, sh, g.epi));
   PI0_CHECK_CUDA(cudaGetLastError());
   ++g_launch_count;
   return 0;
+}
+
+template <int BN, int EPI>
+static int launch_pair(const GemmProblem& g, int num_sms, cudaStream_t stream) {
+  // short-K plain-store tiles (SigLIP q|k|v, out_proj, fc1: K = 1152) are epilogue-bound: 12 epilogue warps, 5 ring stages.
+  // PI0_PAIR_EW3_MAX_K (default 2047; 0 = never) is the largest K that takes that variant.
+  if constexpr (BN == 256 && EPI == EPI_STORE) {
+    static const int max_k = getenv("PI0_PAIR_EW3_MAX_K") ? atoi(getenv("PI0_PAIR_EW3_MAX_K")) : 2047;
+    if (g.K <= max_k) return launch_pair_ew<BN, EPI, 3>(g, num_sms, stream);
+  }
+  return launch_pair_ew<BN, EPI, 2>(g, num_sms, stream);
 }
 
 // The CTA-pair kernel pays off once the single-CTA kernel runs several waves of tiles (the regime where the L2 -> SM
