@@ -16,7 +16,7 @@
 //   pass 2   S_kb again (S_kb+1 is issued BEFORE P.V of block kb, so it runs under the softmax of block kb);
 //            p = rnd(exp(s - M) / L) as bf16 into the 128-byte-swizzled K-major P tile; O += P V_kb (V^T cache
 //            rows staged by TMA through the same ring, M = 128, N = 256 dims, 4 k-blocks of 64 keys)
-//   epilogue O -> rnd -> bf16 -> global (a lane owns a row: 128 contiguous bytes per lane and part)
+//   epilogue O -> rnd -> bf16 -> the idle P tile (four 128-byte-swizzled [128 rows x 64 dims] blocks) -> one TMA store per block
 // Rounding points are those of the chain it replaces: scores and probabilities materialised in bf16, softmax in fp32.
 #include "elementwise.cuh"
 #include "gemm.cuh"
